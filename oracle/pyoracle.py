@@ -1,0 +1,336 @@
+"""ctypes bindings for the CHECKERS — TEST INFRASTRUCTURE, never imported by hivemind_b200/.
+
+* ``Oracle``  : oracle/liboracle.so, our plain-C restatement (oracle/hm_oracle.c).
+* ``Ref``     : oracle/_ref/libhmref.so, the unmodified reference compiled from
+  /root/reference by ``make -C oracle ref`` (exists only where it was built and travels to
+  the GPU box as a prebuilt file).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+import this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "liboracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libhmref.so")
+
+NB_INPUT_VALUES = 4736
+NB_POLICY_VALUES = 4672
+PACKED_DTYPE = np.dtype(
+    [
+        ("pieces", "<u8", (12,)),
+        ("promoted", "<u8", (2,)),
+        ("pocket", "u1", (10,)),
+        ("ep_square", "u1"),
+        ("flags", "u1"),
+        ("last_from", "u1"),
+        ("last_to", "u1"),
+        ("rule50", "u1"),
+        ("repetitions", "u1"),
+    ]
+)
+assert PACKED_DTYPE.itemsize == 128
+POS_DTYPE = np.dtype([("board", PACKED_DTYPE, (2,))])
+assert POS_DTYPE.itemsize == 256
+
+FLAG_STM_BLACK = 0x01
+FLAG_TEAM_BLACK = 0x20
+FLAG_TIME_ADVANTAGE = 0x40
+
+
+class ValueConfig(C.Structure):
+    _fields_ = [
+        ("enable_wdl_eval", C.c_int),
+        ("wdl_value_weight", C.c_float),
+        ("moves_left_discount", C.c_float),
+        ("draw_contempt", C.c_float),
+    ]
+
+    @classmethod
+    def default(cls):
+        # search_params.h:122-128,148
+        return cls(1, 0.25, 0.005, 0.0)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def build_oracle():
+    if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(
+        os.path.join(HERE, "hm_oracle.c")
+    ):
+        subprocess.check_call(["make", "-C", HERE, "oracle"], stdout=subprocess.DEVNULL)
+    return ORACLE_SO
+
+
+class Oracle:
+    """Plain-C restatement (oracle/hm_oracle.c)."""
+
+    def __init__(self):
+        self.lib = C.CDLL(build_oracle())
+        L = self.lib
+        L.hmo_float_to_half.restype = C.c_uint16
+        L.hmo_float_to_half.argtypes = [C.c_float]
+        L.hmo_half_to_float.restype = C.c_float
+        L.hmo_half_to_float.argtypes = [C.c_uint16]
+        L.hmo_float_to_bf16.restype = C.c_uint16
+        L.hmo_float_to_bf16.argtypes = [C.c_float]
+        L.hmo_policy_index.restype = C.c_int32
+        L.hmo_policy_index.argtypes = [C.c_uint32, C.c_int]
+        L.hmo_shape_value.restype = C.c_float
+        L.hmo_shape_value.argtypes = [C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hmo_shape_value_half.restype = C.c_float
+        L.hmo_shape_value_half.argtypes = [C.c_uint16, C.c_void_p, C.c_void_p, C.c_void_p]
+        for name in ("f32", "f16", "bf16", "u8"):
+            getattr(L, f"hmo_encode_planes_{name}").argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        L.hmo_normalize_logits.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        L.hmo_priors_f16.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+        L.hmo_priors_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+        L.hmo_batch_priors_f16.argtypes = [C.c_void_p] * 3 + [C.c_size_t] + [C.c_void_p] * 3
+        L.hmo_policy_tables.argtypes = [C.c_void_p, C.c_void_p]
+        L.hmo_policy_init()
+
+    def encode_planes(self, pos: np.ndarray, dtype: str = "f32") -> np.ndarray:
+        pos = np.ascontiguousarray(pos)
+        n = pos.shape[0]
+        npdt = {"f32": np.float32, "f16": np.uint16, "bf16": np.uint16, "u8": np.uint8}[dtype]
+        out = np.empty((n, 74, 8, 8), npdt)
+        getattr(self.lib, f"hmo_encode_planes_{dtype}")(_ptr(pos), n, _ptr(out))
+        return out
+
+    def policy_tables(self):
+        normal = np.empty((2, 64, 64, 2), np.int32)
+        drop = np.empty((2, 64, 8), np.int32)
+        self.lib.hmo_policy_tables(_ptr(normal), _ptr(drop))
+        return normal, drop
+
+    def policy_index(self, move: int, stm_black: int) -> int:
+        return self.lib.hmo_policy_index(int(move), int(stm_black))
+
+    def normalize_logits(self, logits) -> np.ndarray:
+        l = np.ascontiguousarray(logits, np.float32)
+        out = np.empty_like(l)
+        self.lib.hmo_normalize_logits(_ptr(l), l.size, _ptr(out))
+        return out
+
+    def priors_f16(self, policy_u16, moves, stm_black) -> np.ndarray:
+        p = np.ascontiguousarray(policy_u16, np.uint16)
+        m = np.ascontiguousarray(moves, np.uint32)
+        out = np.empty(m.size, np.float32)
+        self.lib.hmo_priors_f16(_ptr(p), _ptr(m), m.size, int(stm_black), _ptr(out))
+        return out
+
+    def priors_f32(self, policy, moves, stm_black) -> np.ndarray:
+        p = np.ascontiguousarray(policy, np.float32)
+        m = np.ascontiguousarray(moves, np.uint32)
+        out = np.empty(m.size, np.float32)
+        self.lib.hmo_priors_f32(_ptr(p), _ptr(m), m.size, int(stm_black), _ptr(out))
+        return out
+
+    def batch_priors_f16(self, logits_a, logits_b, pos, moves, offsets) -> np.ndarray:
+        la = np.ascontiguousarray(logits_a, np.uint16)
+        lb = np.ascontiguousarray(logits_b, np.uint16)
+        pos = np.ascontiguousarray(pos)
+        m = np.ascontiguousarray(moves, np.uint32)
+        o = np.ascontiguousarray(offsets, np.uint32)
+        out = np.empty(m.size, np.float32)
+        self.lib.hmo_batch_priors_f16(_ptr(la), _ptr(lb), _ptr(pos), pos.shape[0], _ptr(m), _ptr(o), _ptr(out))
+        return out
+
+    def shape_value(self, value, wdl=None, moves_left=None, cfg=None) -> float:
+        cfg = cfg or ValueConfig.default()
+        w = None if wdl is None else np.ascontiguousarray(wdl, np.float32)
+        ml = None if moves_left is None else np.array([moves_left], np.float32)
+        return self.lib.hmo_shape_value(
+            C.c_float(value), None if w is None else _ptr(w), None if ml is None else _ptr(ml), C.byref(cfg)
+        )
+
+    def shape_value_half(self, value_u16, wdl_u16, ml_u16, cfg=None) -> float:
+        cfg = cfg or ValueConfig.default()
+        w = np.ascontiguousarray(wdl_u16, np.uint16)
+        ml = np.array([ml_u16], np.uint16)
+        return self.lib.hmo_shape_value_half(int(value_u16), _ptr(w), _ptr(ml), C.byref(cfg))
+
+
+def ref_available() -> bool:
+    return os.path.exists(REF_SO)
+
+
+class Ref:
+    """The reference itself (oracle/_ref/libhmref.so)."""
+
+    def __init__(self):
+        if not ref_available():
+            raise FileNotFoundError(f"{REF_SO} not built (make -C oracle ref; needs /root/reference)")
+        self.lib = C.CDLL(REF_SO)
+        L = self.lib
+        vp = C.c_void_p
+        L.hmref_board_new.restype = vp
+        L.hmref_board_copy.restype = vp
+        L.hmref_board_copy.argtypes = [vp]
+        L.hmref_board_free.argtypes = [vp]
+        L.hmref_board_set.argtypes = [vp, C.c_char_p]
+        L.hmref_board_set_fen.argtypes = [vp, C.c_int, C.c_char_p]
+        L.hmref_board_fen.argtypes = [vp, C.c_int, C.c_char_p, C.c_int]
+        L.hmref_board_push_uci.argtypes = [vp, C.c_int, C.c_char_p]
+        L.hmref_board_pop.argtypes = [vp, C.c_int]
+        L.hmref_board_make_moves_uci.argtypes = [vp, C.c_char_p, C.c_char_p, vp, vp]
+        L.hmref_board_unmake_moves.argtypes = [vp, C.c_uint32, C.c_uint32]
+        L.hmref_board_stm.argtypes = [vp, C.c_int]
+        L.hmref_board_gives_check.argtypes = [vp, C.c_int, C.c_uint32]
+        for n in ("f32", "f16", "u8"):
+            getattr(L, f"hmref_board_planes_{n}").argtypes = [vp, C.c_int, C.c_int, vp]
+        L.hmref_board_pack.argtypes = [vp, C.c_int, C.c_int, vp]
+        L.hmref_board_legal.argtypes = [vp, C.c_int, vp, C.c_int]
+        L.hmref_board_search_actions.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int]
+        L.hmref_board_move_uci.argtypes = [vp, C.c_int, C.c_uint32, C.c_char_p, C.c_int]
+        L.hmref_board_priors_f16.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]
+        L.hmref_board_priors_f32.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp]
+        L.hmref_normalize_logits.argtypes = [vp, C.c_int, vp]
+        L.hmref_policy_index.argtypes = [C.c_uint32, C.c_int]
+        L.hmref_policy_index_of_label.argtypes = [C.c_char_p]
+        L.hmref_policy_label.argtypes = [C.c_int, C.c_char_p, C.c_int]
+        L.hmref_policy_tables.argtypes = [vp, vp]
+        L.hmref_gen_positions.argtypes = [C.c_uint64, C.c_int, C.POINTER(vp)]
+        L.hmref_time_planes_f16.restype = C.c_double
+        L.hmref_time_planes_f16.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int]
+        L.hmref_time_priors_f16.restype = C.c_double
+        L.hmref_time_priors_f16.argtypes = [C.POINTER(vp), C.c_int, vp, C.c_int, C.c_int]
+        L.hmref_init()
+
+    # -- boards -------------------------------------------------------------------
+    def board(self):
+        return RefBoard(self, self.lib.hmref_board_new())
+
+    def gen_positions(self, seed: int, n: int):
+        arr = (C.c_void_p * n)()
+        self.lib.hmref_gen_positions(seed, n, arr)
+        return [RefBoard(self, arr[i]) for i in range(n)]
+
+    def handles(self, boards):
+        arr = (C.c_void_p * len(boards))()
+        for i, b in enumerate(boards):
+            arr[i] = b.h
+        return arr
+
+    # -- free functions -----------------------------------------------------------
+    def normalize_logits(self, logits):
+        l = np.ascontiguousarray(logits, np.float32)
+        out = np.empty_like(l)
+        self.lib.hmref_normalize_logits(_ptr(l), l.size, _ptr(out))
+        return out
+
+    def policy_index(self, move, stm_black):
+        return self.lib.hmref_policy_index(int(move), int(stm_black))
+
+    def policy_index_of_label(self, label: str):
+        return self.lib.hmref_policy_index_of_label(label.encode())
+
+    def policy_label(self, idx):
+        buf = C.create_string_buffer(16)
+        self.lib.hmref_policy_label(idx, buf, 16)
+        return buf.value.decode()
+
+    def policy_tables(self):
+        normal = np.empty((2, 64, 64, 2), np.int32)
+        drop = np.empty((2, 64, 8), np.int32)
+        self.lib.hmref_policy_tables(_ptr(normal), _ptr(drop))
+        return normal, drop
+
+
+class RefBoard:
+    def __init__(self, ref: Ref, h):
+        self.ref, self.L, self.h = ref, ref.lib, h
+
+    def copy(self):
+        return RefBoard(self.ref, self.L.hmref_board_copy(self.h))
+
+    def set(self, fen_pair: str):
+        assert self.L.hmref_board_set(self.h, fen_pair.encode())
+
+    def set_fen(self, bn: int, fen: str):
+        assert self.L.hmref_board_set_fen(self.h, bn, fen.encode())
+
+    def fen(self, bn):
+        buf = C.create_string_buffer(256)
+        self.L.hmref_board_fen(self.h, bn, buf, 256)
+        return buf.value.decode()
+
+    def push_uci(self, bn: int, uci: str):
+        assert self.L.hmref_board_push_uci(self.h, bn, uci.encode()), uci
+
+    def make_moves_uci(self, a: str, b: str):
+        ma, mb = C.c_uint32(), C.c_uint32()
+        assert self.L.hmref_board_make_moves_uci(self.h, a.encode(), b.encode(), C.byref(ma), C.byref(mb))
+        return ma.value, mb.value
+
+    def unmake_moves(self, ma, mb):
+        self.L.hmref_board_unmake_moves(self.h, ma, mb)
+
+    def stm_black(self, bn):
+        return self.L.hmref_board_stm(self.h, bn)
+
+    def gives_check(self, bn, move):
+        return bool(self.L.hmref_board_gives_check(self.h, bn, move))
+
+    def planes(self, team_black: int, tadv: int, dtype="f32"):
+        npdt = {"f32": np.float32, "f16": np.uint16, "u8": np.uint8}[dtype]
+        out = np.empty((74, 8, 8), npdt)
+        getattr(self.L, f"hmref_board_planes_{dtype}")(self.h, int(team_black), int(tadv), _ptr(out))
+        return out
+
+    def pack(self, team_black: int, tadv: int):
+        out = np.zeros(1, POS_DTYPE)
+        self.L.hmref_board_pack(self.h, int(team_black), int(tadv), _ptr(out))
+        return out
+
+    def legal(self, bn):
+        buf = np.empty(1024, np.uint32)
+        k = self.L.hmref_board_legal(self.h, bn, _ptr(buf), 1024)
+        return buf[:k].copy()
+
+    def search_actions(self, bn, team_black):
+        buf = np.empty(1024, np.uint32)
+        k = self.L.hmref_board_search_actions(self.h, bn, int(team_black), _ptr(buf), 1024)
+        return buf[:k].copy()
+
+    def move_uci(self, bn, move):
+        buf = C.create_string_buffer(16)
+        self.L.hmref_board_move_uci(self.h, bn, int(move), buf, 16)
+        return buf.value.decode()
+
+    def priors_f16(self, bn, policy_u16, moves):
+        p = np.ascontiguousarray(policy_u16, np.uint16)
+        m = np.ascontiguousarray(moves, np.uint32)
+        out = np.empty(m.size, np.float32)
+        self.L.hmref_board_priors_f16(self.h, bn, _ptr(p), _ptr(m), m.size, _ptr(out))
+        return out
+
+    def priors_f32(self, bn, policy, moves):
+        p = np.ascontiguousarray(policy, np.float32)
+        m = np.ascontiguousarray(moves, np.uint32)
+        out = np.empty(m.size, np.float32)
+        self.L.hmref_board_priors_f32(self.h, bn, _ptr(p), _ptr(m), m.size, _ptr(out))
+        return out
+
+
+def gen_config1(ref: Ref, seed: int, n: int):
+    """SURVEY.md §8d config-1 generator: returns (boards, packed[n], moves, offsets[2n+1])."""
+    boards = ref.gen_positions(seed, n)
+    packed = np.zeros(n, POS_DTYPE)
+    moves, offsets = [], [0]
+    for g, b in enumerate(boards):
+        team, tadv = g & 1, (g >> 1) & 1
+        packed[g] = b.pack(team, tadv)[0]
+        for bn in range(2):
+            a = b.search_actions(bn, team)
+            moves.append(a)
+            offsets.append(offsets[-1] + a.size)
+    return boards, packed, np.concatenate(moves).astype(np.uint32), np.array(offsets, np.uint32)
