@@ -1,0 +1,198 @@
+"""Weights ingress for the B200 leaf evaluator.
+
+* ``risev33_spec()``            the layer list of the reference's deployed network
+  (src/architectures/rise_mobile_v3.py:820-849 ``get_rise_v33_model`` with the arguments of
+  src/training/train_loop.py:95-116: WDL + plys heads, shared policy trunk).
+* ``random_state_dict()``       seeded random parameters under the reference's own
+  ``state_dict`` names and shapes (so ``model.load_state_dict(strict=True)`` accepts them);
+  BatchNorm statistics are randomised so that a broken kernel cannot hide behind
+  near-identity normalisation (SURVEY.md §7 hard part 5).
+* ``fold_state_dict()``         BatchNorm folding (eval mode, eps 1e-5) into conv weight + bias,
+  ECA centre tap extraction (builder_util.py:67-80: Conv1d on a length-1 sequence).
+* ``write_hvmw()/read_hvmw()``  the flat container hm_engine_load reads (csrc/hm_net.cu).
+
+numpy only; no torch import.
+"""
+from __future__ import annotations
+
+import struct
+from typing import Dict, List
+
+import numpy as np
+
+ARCH_RISEV33 = 0
+ARCH_CROSSBOARD_RISEV33 = 1
+BN_EPS = 1e-5
+
+
+def risev33_spec() -> dict:
+    kernels = [3] * 15
+    for i in (7, 11, 12, 13):
+        kernels[i] = 5
+    eca = [False] * 15
+    for i in (5, 8, 12, 13, 14):
+        eca[i] = True
+    cops: List[int] = []
+    cop = 256
+    for idx, k in enumerate(kernels):
+        # rise_mobile_v3.py:66-72: 5x5 blocks use channels_operating - 32 * (idx // 2)
+        cops.append(cop - 32 * (idx // 2) if k == 5 else cop)
+        cop += 64
+    return {
+        "arch": ARCH_RISEV33,
+        "in_channels": 74,
+        "channels": 384,
+        "kernels": kernels,
+        "eca": eca,
+        "cops": cops,
+        "value_channels": 16,
+        "value_fc": 512,
+        "policy_channels": 73,
+    }
+
+
+def _bn(rng, c, prefix, sd, gamma_lo=0.5, gamma_hi=1.5):
+    sd[prefix + ".weight"] = rng.uniform(gamma_lo, gamma_hi, c).astype(np.float32)
+    sd[prefix + ".bias"] = (0.1 * rng.standard_normal(c)).astype(np.float32)
+    sd[prefix + ".running_mean"] = (0.1 * rng.standard_normal(c)).astype(np.float32)
+    sd[prefix + ".running_var"] = rng.uniform(0.5, 1.5, c).astype(np.float32)
+    sd[prefix + ".num_batches_tracked"] = np.array(0, np.int64)
+
+
+def _conv(rng, shape, gain=2.0):
+    fan_in = int(np.prod(shape[1:]))
+    return (rng.standard_normal(shape) * np.sqrt(gain / fan_in)).astype(np.float32)
+
+
+def random_state_dict(spec: dict | None = None, seed: int = 0) -> Dict[str, np.ndarray]:
+    """Seeded parameters keyed exactly like the reference RiseV3 ``state_dict``."""
+    spec = spec or risev33_spec()
+    rng = np.random.default_rng(seed)
+    sd: Dict[str, np.ndarray] = {}
+    C = spec["channels"]
+    sd["body_spatial.0.body.0.weight"] = _conv(rng, (C, spec["in_channels"], 3, 3))
+    _bn(rng, C, "body_spatial.0.body.1", sd)
+    for i, (k, cop, eca) in enumerate(zip(spec["kernels"], spec["cops"], spec["eca"])):
+        p = f"body_spatial.{i + 1}."
+        if eca:
+            sd[p + "se.body.0.weight"] = (rng.standard_normal((C, C, 5)) * (6.0 / np.sqrt(C))).astype(np.float32)
+            sd[p + "se.body.0.bias"] = (1.5 + 1.0 * rng.standard_normal(C)).astype(np.float32)
+        sd[p + "body.0.weight"] = _conv(rng, (cop, C, 1, 1))
+        _bn(rng, cop, p + "body.1", sd)
+        sd[p + "body.3.weight"] = _conv(rng, (cop, 1, k, k))
+        _bn(rng, cop, p + "body.4", sd)
+        sd[p + "body.6.weight"] = _conv(rng, (C, cop, 1, 1), gain=1.0)
+        # residual branch kept modest so 15 blocks do not blow the trunk up
+        _bn(rng, C, p + "body.7", sd, gamma_lo=0.3, gamma_hi=0.9)
+    vc = spec["value_channels"]
+    sd["value_head.body.0.weight"] = _conv(rng, (vc, C, 1, 1))
+    _bn(rng, vc, "value_head.body.1", sd)
+    nf = vc * 64
+    sd["value_head.body_wdl.0.weight"] = (rng.standard_normal((3, nf)) * (1.0 / np.sqrt(nf))).astype(np.float32)
+    sd["value_head.body_wdl.0.bias"] = (0.1 * rng.standard_normal(3)).astype(np.float32)
+    sd["value_head.body_plys.0.weight"] = (rng.standard_normal((1, nf)) * (1.5 / np.sqrt(nf))).astype(np.float32)
+    sd["value_head.body_plys.0.bias"] = (0.1 * rng.standard_normal(1)).astype(np.float32)
+    fc = spec["value_fc"]
+    sd["value_head.body_final.0.weight"] = (rng.standard_normal((fc, nf)) / np.sqrt(nf)).astype(np.float32)
+    sd["value_head.body_final.0.bias"] = (0.1 * rng.standard_normal(fc)).astype(np.float32)
+    sd["value_head.body_final.2.weight"] = (rng.standard_normal((1, fc)) / np.sqrt(fc)).astype(np.float32)
+    sd["value_head.body_final.2.bias"] = (0.1 * rng.standard_normal(1)).astype(np.float32)
+    sd["policy_heads.shared_body.0.weight"] = _conv(rng, (C, C, 3, 3))
+    _bn(rng, C, "policy_heads.shared_body.1", sd)
+    pc = spec["policy_channels"]
+    for b in range(2):
+        sd[f"policy_heads.board_projections.{b}.weight"] = _conv(rng, (pc, C, 3, 3), gain=1.2)
+    return sd
+
+
+def _fold(w: np.ndarray, sd, bn_prefix: str):
+    """conv (no bias) followed by eval-mode BatchNorm -> (w', b')."""
+    g = sd[bn_prefix + ".weight"].astype(np.float64)
+    b = sd[bn_prefix + ".bias"].astype(np.float64)
+    m = sd[bn_prefix + ".running_mean"].astype(np.float64)
+    v = sd[bn_prefix + ".running_var"].astype(np.float64)
+    s = g / np.sqrt(v + BN_EPS)
+    wf = w.astype(np.float64) * s.reshape(-1, *([1] * (w.ndim - 1)))
+    return wf.astype(np.float32), (b - m * s).astype(np.float32)
+
+
+def fold_state_dict(sd: Dict[str, np.ndarray], spec: dict | None = None) -> Dict[str, np.ndarray]:
+    """Reference state_dict -> the folded fp32 tensors of the .hvmw container."""
+    spec = spec or risev33_spec()
+    sd = {k: np.asarray(v) for k, v in sd.items()}
+    out: Dict[str, np.ndarray] = {}
+    out["stem.w"], out["stem.b"] = _fold(sd["body_spatial.0.body.0.weight"], sd, "body_spatial.0.body.1")
+    for i, (k, cop, eca) in enumerate(zip(spec["kernels"], spec["cops"], spec["eca"])):
+        p = f"body_spatial.{i + 1}."
+        q = f"b{i}."
+        w, b = _fold(sd[p + "body.0.weight"], sd, p + "body.1")
+        out[q + "pw1.w"], out[q + "pw1.b"] = w.reshape(cop, -1), b
+        w, b = _fold(sd[p + "body.3.weight"], sd, p + "body.4")
+        out[q + "dw.w"], out[q + "dw.b"] = w.reshape(cop, k, k), b
+        w, b = _fold(sd[p + "body.6.weight"], sd, p + "body.7")
+        out[q + "pw2.w"], out[q + "pw2.b"] = w.reshape(w.shape[0], cop), b
+        if eca:
+            ew = sd[p + "se.body.0.weight"]
+            out[q + "eca.w"] = np.ascontiguousarray(ew[:, :, ew.shape[2] // 2]).astype(np.float32)
+            out[q + "eca.b"] = sd[p + "se.body.0.bias"].astype(np.float32)
+    w, b = _fold(sd["value_head.body.0.weight"], sd, "value_head.body.1")
+    out["value.conv.w"], out["value.conv.b"] = w.reshape(w.shape[0], -1), b
+    out["value.wdl.w"] = sd["value_head.body_wdl.0.weight"].astype(np.float32)
+    out["value.wdl.b"] = sd["value_head.body_wdl.0.bias"].astype(np.float32)
+    out["value.plys.w"] = sd["value_head.body_plys.0.weight"].astype(np.float32)
+    out["value.plys.b"] = sd["value_head.body_plys.0.bias"].astype(np.float32)
+    out["policy.shared.w"], out["policy.shared.b"] = _fold(
+        sd["policy_heads.shared_body.0.weight"], sd, "policy_heads.shared_body.1"
+    )
+    out["policy.a.w"] = sd["policy_heads.board_projections.0.weight"].astype(np.float32)
+    out["policy.b.w"] = sd["policy_heads.board_projections.1.weight"].astype(np.float32)
+    return out
+
+
+def write_hvmw(path_or_none, tensors: Dict[str, np.ndarray], arch: int = ARCH_RISEV33) -> bytes:
+    """Serialise folded tensors.  Layout (little endian): 64-byte header
+    ``"HVMW", u32 version=1, u32 arch, u32 n, u64 data_offset``; n entries of 104 bytes
+    ``name[64], u32 dtype(0=f32), u32 ndim, u32 dims[4], u64 offset, u64 nbytes``; data."""
+    names = list(tensors.keys())
+    table_end = 64 + 104 * len(names)
+    data_off = (table_end + 255) // 256 * 256
+    entries, blobs, off = [], [], data_off
+    for n in names:
+        a = np.ascontiguousarray(tensors[n], np.float32)
+        if a.ndim > 4 or len(n.encode()) > 63:
+            raise ValueError(f"cannot store tensor {n}")
+        dims = list(a.shape) + [0] * (4 - a.ndim)
+        entries.append(struct.pack("<64sII4IQQ", n.encode(), 0, a.ndim, *dims, off, a.nbytes))
+        pad = (-a.nbytes) % 256
+        blobs.append(a.tobytes() + b"\0" * pad)
+        off += a.nbytes + pad
+    header = struct.pack("<4sIIIQ", b"HVMW", 1, arch, len(names), data_off).ljust(64, b"\0")
+    raw = header + b"".join(entries)
+    raw = raw.ljust(data_off, b"\0") + b"".join(blobs)
+    if path_or_none is not None:
+        with open(path_or_none, "wb") as f:
+            f.write(raw)
+    return raw
+
+
+def read_hvmw(raw_or_path) -> Dict[str, np.ndarray]:
+    if isinstance(raw_or_path, (bytes, bytearray, memoryview)):
+        raw = bytes(raw_or_path)
+    else:
+        with open(raw_or_path, "rb") as f:
+            raw = f.read()
+    magic, version, arch, n, _ = struct.unpack_from("<4sIIIQ", raw, 0)
+    if magic != b"HVMW" or version != 1:
+        raise ValueError("not an HVMW v1 container")
+    out: Dict[str, np.ndarray] = {}
+    for i in range(n):
+        name, dtype, ndim, d0, d1, d2, d3, off, nbytes = struct.unpack_from("<64sII4IQQ", raw, 64 + 104 * i)
+        dims = (d0, d1, d2, d3)[:ndim]
+        out[name.rstrip(b"\0").decode()] = np.frombuffer(raw, np.float32, nbytes // 4, off).reshape(dims).copy()
+    return out
+
+
+def random_hvmw(seed: int = 0, path=None) -> bytes:
+    """Seeded random-init RISEv3.3 weights as an .hvmw blob (what bench.py loads)."""
+    spec = risev33_spec()
+    return write_hvmw(path, fold_state_dict(random_state_dict(spec, seed), spec), spec["arch"])

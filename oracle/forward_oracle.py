@@ -1,0 +1,131 @@
+"""forward_oracle.py — TEST INFRASTRUCTURE.  CPU fp32 restatement of the reference RISEv3.3
+forward pass on the FOLDED tensors of an .hvmw container (hivemind_b200/weights.py).
+
+Follows, layer by layer:
+  RiseV3.forward                      src/architectures/rise_mobile_v3.py:206-230
+  _Stem                               src/architectures/builder_util.py:154-178
+  _BottlekneckResidualBlock           src/architectures/builder_util.py:445-483
+  _EfficientChannelAttentionModule    src/architectures/builder_util.py:49-80
+  _ValueHead (WDL + plys branch)      src/architectures/builder_util.py:246-326
+  _SharedPolicyHeads                  src/architectures/rise_mobile_v3.py:38-57
+
+Parity status: PINNED against the reference PyTorch module itself —
+tests/test_forward_oracle.py (a) imports the reference model from /root/reference where that
+exists and compares outputs on the same seeded weights, and (b) everywhere checks the committed
+golden outputs in tests/golden/forward_risev33.npz that oracle/make_golden.py produced from the
+reference model.  (The reference's own tests hold no golden network outputs)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import
+this module.
+"""
+from __future__ import annotations
+
+from typing import Dict
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))
+
+
+class ForwardOracle:
+    def __init__(self, tensors: Dict[str, np.ndarray]):
+        self.t = {k: _t(v) for k, v in tensors.items()}
+        self.n_blocks = 0
+        while f"b{self.n_blocks}.pw1.w" in self.t:
+            self.n_blocks += 1
+
+    @torch.no_grad()
+    def forward(self, planes: np.ndarray, return_intermediates: bool = False):
+        """planes: [B,74,8,8] float32.  Returns dict(value[B], wdl[B,3], moves_left[B],
+        pi_a[B,4672], pi_b[B,4672]) as float32 numpy arrays."""
+        t = self.t
+        inter = {}
+        x = _t(planes)
+        # stem: conv3x3 + BN + ReLU (builder_util.py:171-174), BN folded
+        x = F.relu(F.conv2d(x, t["stem.w"], t["stem.b"], padding=1))
+        inter["stem"] = x
+        for i in range(self.n_blocks):
+            q = f"b{i}."
+            if q + "eca.w" in t:
+                # builder_util.py:77-80: avg pool -> Conv1d(k=5,pad=2) on a length-1 sequence
+                # (only the centre tap meets data) -> hard sigmoid -> scale
+                m = x.mean(dim=(2, 3))
+                g = F.hardsigmoid(F.linear(m, t[q + "eca.w"], t[q + "eca.b"]))
+                x = x * g[:, :, None, None]
+            cop = t[q + "pw1.w"].shape[0]
+            k = t[q + "dw.w"].shape[-1]
+            # builder_util.py:465-472
+            y = F.relu(F.conv2d(x, t[q + "pw1.w"][:, :, None, None], t[q + "pw1.b"]))
+            y = F.relu(F.conv2d(y, t[q + "dw.w"][:, None], t[q + "dw.b"], padding=k // 2, groups=cop))
+            y = F.conv2d(y, t[q + "pw2.w"][:, :, None, None], t[q + "pw2.b"])
+            x = x + y  # builder_util.py:483, no activation after the add
+            inter[f"block{i}"] = x
+        # value head (builder_util.py:311-324)
+        v = F.relu(F.conv2d(x, t["value.conv.w"][:, :, None, None], t["value.conv.b"]))
+        inter["value_feat"] = v
+        flat = v.reshape(v.shape[0], -1)
+        wdl = F.linear(flat, t["value.wdl.w"], t["value.wdl.b"])
+        plys = torch.sigmoid(F.linear(flat, t["value.plys.w"], t["value.plys.b"]))
+        sm = torch.softmax(wdl, dim=1)
+        value = sm[:, 2] - sm[:, 0]
+        # shared policy heads (rise_mobile_v3.py:52-57)
+        s = F.relu(F.conv2d(x, t["policy.shared.w"], t["policy.shared.b"], padding=1))
+        inter["policy_shared"] = s
+        pi_a = F.conv2d(s, t["policy.a.w"], None, padding=1).reshape(x.shape[0], -1)
+        pi_b = F.conv2d(s, t["policy.b.w"], None, padding=1).reshape(x.shape[0], -1)
+        out = {
+            "value": value.numpy(),
+            "wdl": wdl.numpy(),
+            "moves_left": plys[:, 0].numpy(),
+            "pi_a": pi_a.numpy(),
+            "pi_b": pi_b.numpy(),
+        }
+        if return_intermediates:
+            out["inter"] = {k: v.numpy() for k, v in inter.items()}
+        return out
+
+
+def reference_model(state_dict: Dict[str, np.ndarray]):
+    """Build the UNMODIFIED reference RiseV3 (needs /root/reference; this container only)
+    and load `state_dict` strictly.  Returns an eval-mode torch module."""
+    import os
+    import sys
+
+    ref = os.environ.get("HM_REFERENCE", "/root/reference")
+    if not os.path.isdir(ref):
+        raise FileNotFoundError(ref)
+    stub = os.path.join(os.path.dirname(os.path.abspath(__file__)), "timm_stub")
+    for p in (ref, stub):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from src.architectures.rise_mobile_v3 import get_rise_v33_model  # noqa: E402
+
+    class Args:  # src/training/train_loop.py:95-116 with use_wdl = use_plys_to_end = True
+        input_shape = (74, 8, 8)
+        n_labels = 0
+        channels_policy_head = 73
+        select_policy_from_plane = True
+        use_wdl = True
+        use_plys_to_end = True
+        use_mlp_wdl_ply = False
+        shared_policy_trunk = True
+
+    model = get_rise_v33_model(Args()).eval()
+    model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in state_dict.items()}, strict=True)
+    return model
+
+
+@torch.no_grad()
+def reference_forward(model, planes: np.ndarray):
+    value, (pi_a, pi_b), _aux, wdl, plys = model(_t(planes))
+    return {
+        "value": value[:, 0].numpy(),
+        "wdl": wdl.numpy(),
+        "moves_left": plys[:, 0].numpy(),
+        "pi_a": pi_a.numpy(),
+        "pi_b": pi_b.numpy(),
+    }
