@@ -427,19 +427,20 @@ int hm_engine_debug_fetch(hm_engine* h, size_t worker, const char* name, float* 
                           size_t cap_floats, size_t* n_floats) {
     HM_TRY
     Worker* w = get_worker(h, worker);
-    if (!w || !use_device(h) || !name || !out) return 0;
+    if (!w || !use_device(h) || !name) return 0;
     auto it = w->debug_views.find(name);
     if (it == w->debug_views.end()) { set_error(std::string("unknown activation ") + name); return 0; }
     const size_t rows = it->second.second[0], cols = it->second.second[1];
     const bool f32 = it->second.second[2] != 0;
     const size_t count = rows * cols;
     if (n_floats) *n_floats = count;
+    if (cap_floats == 0) return 1;  // size query
     if (count > cap_floats) { set_error("debug buffer too small"); return 0; }
     if (!cuda_ok(cudaStreamSynchronize(w->stream), "sync")) return 0;
     if (f32) return cuda_ok(cudaMemcpy(out, it->second.first, count * 4, cudaMemcpyDeviceToHost), "D2H") ? 1 : 0;
-    std::vector<__nv_bfloat16> tmp(count);
+    std::vector<act_t> tmp(count);
     if (!cuda_ok(cudaMemcpy(tmp.data(), it->second.first, count * 2, cudaMemcpyDeviceToHost), "D2H")) return 0;
-    for (size_t i = 0; i < count; ++i) out[i] = __bfloat162float(tmp[i]);
+    for (size_t i = 0; i < count; ++i) out[i] = act_to_float(tmp[i]);
     return 1;
     HM_CATCH(0)
 }

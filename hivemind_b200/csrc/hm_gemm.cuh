@@ -5,10 +5,10 @@
 //   out[m, n] = act( sum_{tap, c} A[pos(m), y(m)+dy(tap), x(m)+dx(tap), c] * W[n, tap*Cpad + c]
 //                    + bias[n] ) (+ residual[m, n])
 //
-// A is an NHWC bf16 activation [B, 8, 8, C] seen through a 4-D TMA tensor map
+// A is an NHWC 16-bit activation [B, 8, 8, C] seen through a 4-D TMA tensor map
 // (dims C, x, y, pos); a k x k convolution is `taps = k*k` shifted box loads whose
 // out-of-board parts TMA zero-fills, i.e. the conv zero padding costs nothing and no
-// im2col buffer exists.  W is bf16 [N, taps*Cpad] (K-major), bias fp32 (BatchNorm folded).
+// im2col buffer exists.  W is 16-bit [N, taps*Cpad] (K-major), bias fp32 (BatchNorm folded).
 //
 // CTA = 128 output rows (two positions) x BN columns, 192 threads:
 //   warp 0     TMA producer (one elected lane)
@@ -28,9 +28,9 @@ struct GemmParams {
     int ksize;         // 1, 3 or 5
     int kchunks;       // 64-wide K chunks per tap = Cpad / 64
     const float* bias; // [n_valid] or nullptr
-    const __nv_bfloat16* residual; // [M, ldr] or nullptr
+    const act_t* residual; // [M, ldr] or nullptr
     int ldr;
-    void* out;         // bf16 or fp32 [M, ldc]
+    void* out;         // act_t or fp32 [M, ldc]
     int ldc;
     int relu;
     int out_f32;
@@ -122,7 +122,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
     } else if (warp == 1) {
         // ===== MMA issuer =====
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN);
+            constexpr uint32_t idesc = umma_idesc_16(GEMM_BM, BN, UMMA_FMT_16);
             int stage = 0;
             uint32_t phase = 0;
             for (int it = 0; it < k_iters; ++it) {
@@ -177,8 +177,8 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                 for (int q = 0; q < 4; ++q) {
                     if (q * 8 < ncols) {
                         const uint4 rv = __ldg(r + q);
-                        const float2 f0 = unpack_bf16x2(rv.x), f1 = unpack_bf16x2(rv.y),
-                                     f2 = unpack_bf16x2(rv.z), f3 = unpack_bf16x2(rv.w);
+                        const float2 f0 = unpack_act2(rv.x), f1 = unpack_act2(rv.y),
+                                     f2 = unpack_act2(rv.z), f3 = unpack_act2(rv.w);
                         v[q * 8 + 0] += f0.x; v[q * 8 + 1] += f0.y;
                         v[q * 8 + 2] += f1.x; v[q * 8 + 3] += f1.y;
                         v[q * 8 + 4] += f2.x; v[q * 8 + 5] += f2.y;
@@ -194,16 +194,16 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                     if (q * 4 < ncols)
                         o[q] = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
             } else {
-                uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) +
+                uint4* o = reinterpret_cast<uint4*>(static_cast<act_t*>(p.out) +
                                                     static_cast<size_t>(row) * p.ldc + n0 + c0);
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
                     if (q * 8 < ncols) {
                         uint4 w;
-                        w.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]);
-                        w.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
-                        w.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]);
-                        w.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+                        w.x = pack_act2(v[q * 8 + 0], v[q * 8 + 1]);
+                        w.y = pack_act2(v[q * 8 + 2], v[q * 8 + 3]);
+                        w.z = pack_act2(v[q * 8 + 4], v[q * 8 + 5]);
+                        w.w = pack_act2(v[q * 8 + 6], v[q * 8 + 7]);
                         o[q] = w;
                     }
             }
@@ -214,7 +214,7 @@ gemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmA,
                 const int pos = row >> 6;
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    float s = p.out_f32 ? v[j] : __bfloat162float(__float2bfloat16_rn(v[j]));
+                    float s = p.out_f32 ? v[j] : act_to_float(float_to_act(v[j]));
                     s += __shfl_xor_sync(0xffffffffu, s, 16);
                     s += __shfl_xor_sync(0xffffffffu, s, 8);
                     s += __shfl_xor_sync(0xffffffffu, s, 4);

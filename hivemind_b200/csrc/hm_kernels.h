@@ -5,6 +5,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include "../../include/hm_engine.h"
+#include "hm_act.h"
 
 namespace hm {
 
@@ -14,25 +15,25 @@ constexpr int POLICY_LD = 160;      // 2 x 73 policy channels padded to a multip
 // ---- stage P ------------------------------------------------------------------------
 // packed positions -> [n,74,8,8] (NCHW) in dtype HM_DTYPE_* (planes.cc:213-265)
 void launch_planes_nchw(const hm_packed_pos* pos, int n, void* out, int dtype, cudaStream_t s);
-// packed positions -> [n,64,80] bf16 NHWC (network input layout; channels 74..79 zero)
-void launch_planes_nhwc(const hm_packed_pos* pos, int n, __nv_bfloat16* out, cudaStream_t s);
-// dense fp16 NCHW planes -> bf16 NHWC (reference-shaped entry, engine.cc:598-602 input)
-void launch_planes_f16_to_nhwc(const __half* in, int n, __nv_bfloat16* out, cudaStream_t s);
+// packed positions -> [n,64,80] 16-bit NHWC (network input layout; channels 74..79 zero)
+void launch_planes_nhwc(const hm_packed_pos* pos, int n, act_t* out, cudaStream_t s);
+// dense fp16 NCHW planes -> 16-bit NHWC (reference-shaped entry, engine.cc:598-602 input)
+void launch_planes_f16_to_nhwc(const __half* in, int n, act_t* out, cudaStream_t s);
 
 // ---- stage F, bandwidth-bound layers ------------------------------------------------------
-// depthwise k x k + folded BN + ReLU on [n,64,C] bf16 (builder_util.py:468-470)
+// depthwise k x k + folded BN + ReLU on [n,64,C] 16-bit (builder_util.py:468-470)
 // w: [k*k][C] fp32 (tap-major), b: [C] fp32
-void launch_depthwise(const __nv_bfloat16* in, __nv_bfloat16* out, const float* w, const float* b,
+void launch_depthwise(const act_t* in, act_t* out, const float* w, const float* b,
                       int n, int C, int ksize, cudaStream_t s);
 // ECA (builder_util.py:49-80 with hard sigmoid): x[n,64,384] -> x * hardsigmoid(Wc*mean(x)+b)
-// wt: [384 in][384 out] bf16 (centre tap, transposed), b: [384] fp32.  in may equal out.
-void launch_eca(const __nv_bfloat16* in, __nv_bfloat16* out, const __nv_bfloat16* wt,
+// wt: [384 in][384 out] 16-bit (centre tap, transposed), b: [384] fp32.  in may equal out.
+void launch_eca(const act_t* in, act_t* out, const act_t* wt,
                 const float* b, int n, cudaStream_t s);
-// value head tail (builder_util.py:311-324): feat [n,64,16] bf16 (after conv+BN+ReLU),
+// value head tail (builder_util.py:311-324): feat [n,64,16] 16-bit (after conv+BN+ReLU),
 // w4: [64 sq][16 c][4] fp32 (3 wdl rows + plys row, from Linear weights indexed c*64+sq),
 // b4: [4].  raw5: [n,5] fp32 {value, wdl_loss, wdl_draw, wdl_win, moves_left};
 // half outputs may be null.
-void launch_value_tail(const __nv_bfloat16* feat, const float* w4, const float* b4, int n,
+void launch_value_tail(const act_t* feat, const float* w4, const float* b4, int n,
                        float* raw5, __half* value_h, __half* wdl_h, __half* ml_h,
                        cudaStream_t s);
 // policy logits [n*64, POLICY_LD] fp32 (col = board*73 + ch) -> fp16 [n,4672] x2, idx = ch*64+sq

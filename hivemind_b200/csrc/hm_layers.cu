@@ -1,6 +1,6 @@
 // hm_layers.cu — the bandwidth-bound layers of RISEv3 (SURVEY.md §8a rows F2b, F3, F4 tail,
 // F6): depthwise k x k + BN + ReLU, ECA squeeze/excite, value-head tail, policy layout.
-// Activations are NHWC bf16: x[pos][sq][C], sq = rank*8 + file.
+// Activations are NHWC 16-bit: x[pos][sq][C], sq = rank*8 + file.
 #include "hm_kernels.h"
 #include "hm_ptx.cuh"
 
@@ -8,7 +8,7 @@ namespace hm {
 
 // ---------------------------------------------------------------------------------------
 // Depthwise conv (reference: builder_util.py:468-470, Conv2d(groups=C) + BN + ReLU).
-// Block = one position x 64 channels: the 64x64 bf16 tile (8 KB) is staged in shared memory
+// Block = one position x 64 channels: the 64x64 16-bit tile (8 KB) is staged in shared memory
 // once, every output reads its k*k neighbours from there; one work item = one square x 8
 // channels (16-byte load/store).  Reads and writes each element of the operating tensor
 // exactly once from/to global memory.
@@ -18,16 +18,16 @@ constexpr int DW_THREADS = 256;
 
 template <int KS>
 __global__ void __launch_bounds__(DW_THREADS)
-depthwise_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+depthwise_kernel(const act_t* __restrict__ in, act_t* __restrict__ out,
                  const float* __restrict__ w, const float* __restrict__ bias, int C) {
-    __shared__ __align__(16) __nv_bfloat16 tile[64][DW_CH];      // [sq][ch]
+    __shared__ __align__(16) act_t tile[64][DW_CH];      // [sq][ch]
     __shared__ __align__(16) float ws[KS * KS][DW_CH];
     __shared__ __align__(16) float bs[DW_CH];
     const int pos = blockIdx.x;
     const int c0 = blockIdx.y * DW_CH;
     const int cw = min(DW_CH, C - c0);  // multiple of 8
     const int groups = cw >> 3;
-    const __nv_bfloat16* src = in + static_cast<size_t>(pos) * 64 * C + c0;
+    const act_t* src = in + static_cast<size_t>(pos) * 64 * C + c0;
     for (int it = threadIdx.x; it < 64 * 8; it += DW_THREADS) {
         const int sq = it >> 3, g = it & 7;
         if (g < groups)
@@ -41,7 +41,7 @@ depthwise_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict
     if (threadIdx.x < DW_CH) bs[threadIdx.x] = threadIdx.x < cw ? __ldg(bias + c0 + threadIdx.x) : 0.0f;
     __syncthreads();
 
-    __nv_bfloat16* dst = out + static_cast<size_t>(pos) * 64 * C + c0;
+    act_t* dst = out + static_cast<size_t>(pos) * 64 * C + c0;
     constexpr int H = KS / 2;
     for (int it = threadIdx.x; it < 64 * 8; it += DW_THREADS) {
         const int sq = it >> 3, g = it & 7;
@@ -61,8 +61,8 @@ depthwise_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict
                 const uint4 v = *reinterpret_cast<const uint4*>(&tile[yy * 8 + xx][g * 8]);
                 const float4 w0 = *reinterpret_cast<const float4*>(&ws[ky * KS + kx][g * 8]);
                 const float4 w1 = *reinterpret_cast<const float4*>(&ws[ky * KS + kx][g * 8 + 4]);
-                const float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y),
-                             c = unpack_bf16x2(v.z), d = unpack_bf16x2(v.w);
+                const float2 a = unpack_act2(v.x), b = unpack_act2(v.y),
+                             c = unpack_act2(v.z), d = unpack_act2(v.w);
                 acc[0] = fmaf(a.x, w0.x, acc[0]); acc[1] = fmaf(a.y, w0.y, acc[1]);
                 acc[2] = fmaf(b.x, w0.z, acc[2]); acc[3] = fmaf(b.y, w0.w, acc[3]);
                 acc[4] = fmaf(c.x, w1.x, acc[4]); acc[5] = fmaf(c.y, w1.y, acc[5]);
@@ -70,15 +70,15 @@ depthwise_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict
             }
         }
         uint4 o;
-        o.x = pack_bf16x2(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f));
-        o.y = pack_bf16x2(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
-        o.z = pack_bf16x2(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
-        o.w = pack_bf16x2(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
+        o.x = pack_act2(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f));
+        o.y = pack_act2(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
+        o.z = pack_act2(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
+        o.w = pack_act2(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
         *reinterpret_cast<uint4*>(dst + static_cast<size_t>(sq) * C + g * 8) = o;
     }
 }
 
-void launch_depthwise(const __nv_bfloat16* in, __nv_bfloat16* out, const float* w, const float* b,
+void launch_depthwise(const act_t* in, act_t* out, const float* w, const float* b,
                       int n, int C, int ksize, cudaStream_t s) {
     if (n <= 0) return;
     dim3 grid(n, (C + DW_CH - 1) / DW_CH);
@@ -95,18 +95,18 @@ constexpr int ECA_C = 384;
 constexpr int ECA_P = 4;
 
 __global__ void __launch_bounds__(ECA_C)
-eca_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
-           const __nv_bfloat16* __restrict__ wt, const float* __restrict__ bias, int n) {
+eca_kernel(const act_t* __restrict__ in, act_t* __restrict__ out,
+           const act_t* __restrict__ wt, const float* __restrict__ bias, int n) {
     __shared__ float mean_s[ECA_P][ECA_C];
     __shared__ float gate_s[ECA_P][ECA_C];
     const int p0 = blockIdx.x * ECA_P;
     const int np = min(ECA_P, n - p0);
     const int c = threadIdx.x;
     for (int p = 0; p < np; ++p) {
-        const __nv_bfloat16* x = in + static_cast<size_t>(p0 + p) * 64 * ECA_C + c;
+        const act_t* x = in + static_cast<size_t>(p0 + p) * 64 * ECA_C + c;
         float s = 0.0f;
 #pragma unroll 8
-        for (int sq = 0; sq < 64; ++sq) s += __bfloat162float(x[static_cast<size_t>(sq) * ECA_C]);
+        for (int sq = 0; sq < 64; ++sq) s += act_to_float(x[static_cast<size_t>(sq) * ECA_C]);
         mean_s[p][c] = s * (1.0f / 64.0f);  // AdaptiveAvgPool2d(1)
     }
     __syncthreads();
@@ -114,7 +114,7 @@ eca_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out
 #pragma unroll
     for (int p = 0; p < ECA_P; ++p) acc[p] = 0.0f;
     for (int k = 0; k < ECA_C; ++k) {
-        const float wv = __bfloat162float(wt[static_cast<size_t>(k) * ECA_C + c]);
+        const float wv = act_to_float(wt[static_cast<size_t>(k) * ECA_C + c]);
 #pragma unroll
         for (int p = 0; p < ECA_P; ++p) acc[p] = fmaf(wv, mean_s[p][k], acc[p]);
     }
@@ -133,19 +133,19 @@ eca_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out
             const int g = i % (ECA_C / 8);
             const uint4 v = xi[i];
             const float* gs = &gate_s[p][g * 8];
-            float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y), cc = unpack_bf16x2(v.z),
-                   d = unpack_bf16x2(v.w);
+            float2 a = unpack_act2(v.x), b = unpack_act2(v.y), cc = unpack_act2(v.z),
+                   d = unpack_act2(v.w);
             uint4 o;
-            o.x = pack_bf16x2(a.x * gs[0], a.y * gs[1]);
-            o.y = pack_bf16x2(b.x * gs[2], b.y * gs[3]);
-            o.z = pack_bf16x2(cc.x * gs[4], cc.y * gs[5]);
-            o.w = pack_bf16x2(d.x * gs[6], d.y * gs[7]);
+            o.x = pack_act2(a.x * gs[0], a.y * gs[1]);
+            o.y = pack_act2(b.x * gs[2], b.y * gs[3]);
+            o.z = pack_act2(cc.x * gs[4], cc.y * gs[5]);
+            o.w = pack_act2(d.x * gs[6], d.y * gs[7]);
             xo[i] = o;
         }
     }
 }
 
-void launch_eca(const __nv_bfloat16* in, __nv_bfloat16* out, const __nv_bfloat16* wt,
+void launch_eca(const act_t* in, act_t* out, const act_t* wt,
                 const float* b, int n, cudaStream_t s) {
     if (n <= 0) return;
     eca_kernel<<<(n + ECA_P - 1) / ECA_P, ECA_C, 0, s>>>(in, out, wt, b, n);
@@ -157,7 +157,7 @@ void launch_eca(const __nv_bfloat16* in, __nv_bfloat16* out, const __nv_bfloat16
 // One warp per position; lane handles squares lane and lane+32.
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
-value_tail_kernel(const __nv_bfloat16* __restrict__ feat, const float* __restrict__ w4,
+value_tail_kernel(const act_t* __restrict__ feat, const float* __restrict__ w4,
                   const float* __restrict__ b4, int n, float* __restrict__ raw5,
                   __half* __restrict__ value_h, __half* __restrict__ wdl_h,
                   __half* __restrict__ ml_h) {
@@ -174,7 +174,7 @@ value_tail_kernel(const __nv_bfloat16* __restrict__ feat, const float* __restric
         const float4* wp = reinterpret_cast<const float4*>(w4 + static_cast<size_t>(sq) * 16 * 4);
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-            const float2 x = unpack_bf16x2(u[q]);
+            const float2 x = unpack_act2(u[q]);
             const float4 wa = __ldg(wp + 2 * q), wb = __ldg(wp + 2 * q + 1);
             acc[0] = fmaf(x.x, wa.x, acc[0]); acc[1] = fmaf(x.x, wa.y, acc[1]);
             acc[2] = fmaf(x.x, wa.z, acc[2]); acc[3] = fmaf(x.x, wa.w, acc[3]);
@@ -207,7 +207,7 @@ value_tail_kernel(const __nv_bfloat16* __restrict__ feat, const float* __restric
     }
 }
 
-void launch_value_tail(const __nv_bfloat16* feat, const float* w4, const float* b4, int n,
+void launch_value_tail(const act_t* feat, const float* w4, const float* b4, int n,
                        float* raw5, __half* value_h, __half* wdl_h, __half* ml_h,
                        cudaStream_t s) {
     if (n <= 0) return;

@@ -89,7 +89,7 @@ static bool make_tm_weights(CUtensorMap* tm, const void* w, int rows, int kcols,
     cuuint64_t strides[1] = {static_cast<cuuint64_t>(kcols) * 2};
     cuuint32_t box[2] = {64, static_cast<cuuint32_t>(box_rows)};
     cuuint32_t es[2] = {1, 1};
-    CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w), dims, strides,
+    CUresult r = g_encode(tm, HM_TMA_DTYPE, 2, const_cast<void*>(w), dims, strides,
                           box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(W) failed: " + std::to_string(r)); return false; }
@@ -103,7 +103,7 @@ static bool make_tm_act(CUtensorMap* tm, const void* x, int n, int C) {
                              static_cast<cuuint64_t>(C) * 128};
     cuuint32_t box[4] = {64, 8, 8, 2};
     cuuint32_t es[4] = {1, 1, 1, 1};
-    CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides,
+    CUresult r = g_encode(tm, HM_TMA_DTYPE, 4, const_cast<void*>(x), dims, strides,
                           box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(A) failed: " + std::to_string(r)); return false; }
@@ -130,15 +130,15 @@ constexpr int GEMM_STAGES = 3;
 // conv weight [cout][cin][k][k] fp32 (+ optional bias [cout]) -> bf16 [n_rows][k*k*cpad],
 // K index = tap*cpad + c with tap = ky*k + kx (cross-correlation: in[y+ky-k/2][x+kx-k/2]).
 // `row_offset`/`dst` let two convs share one padded matrix (policy projections A|B).
-static void pack_conv(std::vector<__nv_bfloat16>& dst, int ktot, int cpad, const float* w, int cout,
+static void pack_conv(std::vector<act_t>& dst, int ktot, int cpad, const float* w, int cout,
                       int cin, int k, int row_offset) {
     for (int o = 0; o < cout; ++o)
         for (int c = 0; c < cin; ++c)
             for (int t = 0; t < k * k; ++t)
                 dst[static_cast<size_t>(row_offset + o) * ktot + t * cpad + c] =
-                    __float2bfloat16(w[(static_cast<size_t>(o) * cin + c) * k * k + t]);
+                    float_to_act(w[(static_cast<size_t>(o) * cin + c) * k * k + t]);
 }
-static bool finish_dense(Net& net, DenseLayer& L, const std::vector<__nv_bfloat16>& w,
+static bool finish_dense(Net& net, DenseLayer& L, const std::vector<act_t>& w,
                          const std::vector<float>* bias) {
     L.w = upload(net, w);
     if (!L.w) return false;
@@ -161,7 +161,7 @@ static bool make_dense(Net& net, DenseLayer& L, const std::string& name, const H
     L.n_rows = round_up(L.cout, GEMM_BN);
     L.n_valid = round_up(L.cout, 8);
     const int ktot = L.ksize * L.ksize * L.cpad;
-    std::vector<__nv_bfloat16> packed(static_cast<size_t>(L.n_rows) * ktot, __float2bfloat16(0.0f));
+    std::vector<act_t> packed(static_cast<size_t>(L.n_rows) * ktot, float_to_act(0.0f));
     pack_conv(packed, ktot, L.cpad, w->data, L.cout, L.cin, L.ksize, 0);
     std::vector<float> bias;
     if (b) bias.assign(b->data, b->data + b->numel());
@@ -210,9 +210,9 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
                 return nullptr;
             }
             blk.eca = true;
-            std::vector<__nv_bfloat16> wt(384 * 384);
+            std::vector<act_t> wt(384 * 384);
             for (int o = 0; o < 384; ++o)
-                for (int k = 0; k < 384; ++k) wt[k * 384 + o] = __float2bfloat16(ew->data[o * 384 + k]);
+                for (int k = 0; k < 384; ++k) wt[k * 384 + o] = float_to_act(ew->data[o * 384 + k]);
             blk.eca_wt = upload(*net, wt);
             blk.eca_b = upload(*net, std::vector<float>(eb->data, eb->data + 384));
             net->param_count += ew->numel() + eb->numel();
@@ -259,7 +259,7 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
         L.n_rows = round_up(POLICY_LD, GEMM_BN);
         L.n_valid = POLICY_LD;
         const int ktot = L.ksize * L.ksize * L.cpad;
-        std::vector<__nv_bfloat16> packed(static_cast<size_t>(L.n_rows) * ktot, __float2bfloat16(0.0f));
+        std::vector<act_t> packed(static_cast<size_t>(L.n_rows) * ktot, float_to_act(0.0f));
         pack_conv(packed, ktot, L.cpad, pa->data, 73, L.cin, L.ksize, 0);
         pack_conv(packed, ktot, L.cpad, pb->data, 73, L.cin, L.ksize, 73);
         net->param_count += pa->numel() + pb->numel();
@@ -301,9 +301,9 @@ static bool gemm_prepare() {
 }
 
 // One dense layer as an Op: in = NHWC bf16 [n][64][cin_buf] -> out [n*64][ldc].
-static bool add_dense(std::vector<Op>& ops, const DenseLayer& L, const __nv_bfloat16* in,
+static bool add_dense(std::vector<Op>& ops, const DenseLayer& L, const act_t* in,
                       int cin_buf, int n_pos, void* out, int ldc, bool relu, bool out_f32,
-                      const __nv_bfloat16* residual, int ldr) {
+                      const act_t* residual, int ldr) {
     CUtensorMap tm_a;
     if (!make_tm_act(&tm_a, in, n_pos, cin_buf)) return false;
     GemmParams p{};
@@ -382,14 +382,14 @@ static bool setup_worker(Engine* e, Worker& w) {
     w.debug_views["stem"] = {w.d_trunk[cur], {static_cast<int>(rows), 384, 0}};
     for (size_t i = 0; i < net.blocks.size(); ++i) {
         const Block& b = net.blocks[i];
-        __nv_bfloat16* x = w.d_trunk[cur];
-        __nv_bfloat16* y = w.d_trunk[cur ^ 1];
+        act_t* x = w.d_trunk[cur];
+        act_t* y = w.d_trunk[cur ^ 1];
         if (b.eca) {
             Op op;
             op.name = "b" + std::to_string(i) + ".eca";
             op.klass = "eca";
             op.bytes = 2.0 * rows * 384 * 2;
-            const __nv_bfloat16* wt = b.eca_wt;
+            const act_t* wt = b.eca_wt;
             const float* eb = b.eca_b;
             op.launch = [x, wt, eb, B](cudaStream_t s) { launch_eca(x, x, wt, eb, B, s); };
             ops.push_back(std::move(op));
@@ -400,8 +400,8 @@ static bool setup_worker(Engine* e, Worker& w) {
             op.name = "b" + std::to_string(i) + ".dw" + std::to_string(b.ksize);
             op.klass = "depthwise";
             op.bytes = 2.0 * rows * b.cop * 2;
-            const __nv_bfloat16* in = w.d_exp[0];
-            __nv_bfloat16* out = w.d_exp[1];
+            const act_t* in = w.d_exp[0];
+            act_t* out = w.d_exp[1];
             const float *dw = b.dw_w, *db = b.dw_b;
             const int cop = b.cop, ks = b.ksize;
             op.launch = [in, out, dw, db, B, cop, ks](cudaStream_t s) { launch_depthwise(in, out, dw, db, B, cop, ks, s); };
@@ -413,7 +413,7 @@ static bool setup_worker(Engine* e, Worker& w) {
     }
     // NOTE: trunk buffers ping-pong, so only the LAST writer of each buffer is inspectable
     // after a pass; "trunk" is the final activation.
-    __nv_bfloat16* trunk = w.d_trunk[cur];
+    act_t* trunk = w.d_trunk[cur];
     w.debug_views["trunk"] = {trunk, {static_cast<int>(rows), 384, 0}};
     if (!add_dense(ops, net.value_conv, trunk, 384, B, w.d_vfeat, 16, true, false, nullptr, 0)) return false;
     w.debug_views["value_feat"] = {w.d_vfeat, {static_cast<int>(rows), 16, 0}};
@@ -422,7 +422,7 @@ static bool setup_worker(Engine* e, Worker& w) {
         op.name = "value.tail";
         op.klass = "head";
         op.bytes = static_cast<double>(rows) * 16 * 2;
-        const __nv_bfloat16* f = w.d_vfeat;
+        const act_t* f = w.d_vfeat;
         const float *w4 = net.value_w4, *b4 = net.value_b4;
         float* raw5 = w.d_raw5;
         __half *vh = w.d_value_h, *wh = w.d_wdl_h, *mh = w.d_ml_h;
@@ -444,7 +444,7 @@ static bool setup_worker(Engine* e, Worker& w) {
         op.klass = "planes";
         op.bytes = static_cast<double>(B) * (HM_NB_INPUT_VALUES * 2 + 64 * PLANES_NHWC_C * 2);
         const __half* in = w.d_obs;
-        __nv_bfloat16* out = w.d_planes;
+        act_t* out = w.d_planes;
         op.launch = [in, out, B](cudaStream_t s) { launch_planes_f16_to_nhwc(in, B, out, s); };
         w.ops_dense_in.push_back(std::move(op));
     }
@@ -465,7 +465,7 @@ static bool setup_worker(Engine* e, Worker& w) {
         op.klass = "planes";
         op.bytes = static_cast<double>(B) * (256 + 64 * PLANES_NHWC_C * 2);
         const hm_packed_pos* pp = w.d_pos;
-        __nv_bfloat16* out = w.d_planes;
+        act_t* out = w.d_planes;
         op.launch = [pp, out, B](cudaStream_t s) { launch_planes_nhwc(pp, B, out, s); };
         w.ops_fused_in.push_back(std::move(op));
     }

@@ -11,6 +11,7 @@
 #include <string>
 #include <vector>
 #include "../../include/hm_engine.h"
+#include "hm_act.h"
 
 namespace hm {
 
@@ -43,7 +44,7 @@ struct DenseLayer {            // one tcgen05 GEMM layer (1x1 or kxk convolution
     int cpad = 0;              // cin rounded up to 64 (K columns per tap)
     int n_rows = 0;            // cout rounded up to 128 (rows of the padded W)
     int n_valid = 0;           // columns stored by the epilogue (multiple of 8)
-    __nv_bfloat16* w = nullptr;  // [n_rows][taps*cpad]
+    act_t* w = nullptr;  // [n_rows][taps*cpad]
     float* bias = nullptr;       // [n_valid] or null
     CUtensorMap tm_w;
     double macs_per_pos() const { return 64.0 * cin * cout * ksize * ksize; }
@@ -54,7 +55,7 @@ struct Block {
     DenseLayer pw1, pw2;
     float* dw_w = nullptr;  // [k*k][cop]
     float* dw_b = nullptr;  // [cop]
-    __nv_bfloat16* eca_wt = nullptr;  // [384 in][384 out]
+    act_t* eca_wt = nullptr;  // [384 in][384 out]
     float* eca_b = nullptr;
 };
 struct Net {
@@ -97,12 +98,12 @@ struct Worker {
     float* d_priors = nullptr;
     float* d_values = nullptr;
     __half* d_obs = nullptr;
-    __nv_bfloat16* d_planes = nullptr;
-    __nv_bfloat16* d_trunk[2] = {nullptr, nullptr};
-    __nv_bfloat16* d_exp[2] = {nullptr, nullptr};
-    __nv_bfloat16* d_pol_shared = nullptr;
+    act_t* d_planes = nullptr;
+    act_t* d_trunk[2] = {nullptr, nullptr};
+    act_t* d_exp[2] = {nullptr, nullptr};
+    act_t* d_pol_shared = nullptr;
     float* d_logits = nullptr;
-    __nv_bfloat16* d_vfeat = nullptr;
+    act_t* d_vfeat = nullptr;
     float* d_raw5 = nullptr;
     __half *d_value_h = nullptr, *d_wdl_h = nullptr, *d_ml_h = nullptr, *d_pi_a = nullptr,
            *d_pi_b = nullptr;

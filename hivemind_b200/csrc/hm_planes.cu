@@ -103,9 +103,9 @@ planes_nchw_kernel(const hm_packed_pos* __restrict__ pos, int n, T* __restrict__
     }
 }
 
-// NHWC bf16 [n][64][80]: one work item = 8 consecutive channels of one square (16-byte store).
+// NHWC 16-bit [n][64][80]: one work item = 8 consecutive channels of one square (16-byte store).
 __global__ void __launch_bounds__(PL_THREADS)
-planes_nhwc_kernel(const hm_packed_pos* __restrict__ pos, int n, __nv_bfloat16* __restrict__ out) {
+planes_nhwc_kernel(const hm_packed_pos* __restrict__ pos, int n, act_t* __restrict__ out) {
     __shared__ __align__(16) hm_packed_pos s_pos[PL_POS_PER_BLOCK];
     const int p0 = blockIdx.x * PL_POS_PER_BLOCK;
     load_records(pos, p0, n, s_pos);
@@ -132,15 +132,15 @@ planes_nhwc_kernel(const hm_packed_pos* __restrict__ pos, int n, __nv_bfloat16* 
             }
         }
         uint4 w;
-        w.x = pack_bf16x2(v[0], v[1]); w.y = pack_bf16x2(v[2], v[3]);
-        w.z = pack_bf16x2(v[4], v[5]); w.w = pack_bf16x2(v[6], v[7]);
+        w.x = pack_act2(v[0], v[1]); w.y = pack_act2(v[2], v[3]);
+        w.z = pack_act2(v[4], v[5]); w.w = pack_act2(v[6], v[7]);
         reinterpret_cast<uint4*>(out + (static_cast<size_t>(p0 + pl) * 64 + sq) * PLANES_NHWC_C)[g] = w;
     }
 }
 
-// dense fp16 NCHW [n][74][64] -> bf16 NHWC [n][64][80], through a shared-memory transpose
+// dense fp16 NCHW [n][74][64] -> 16-bit NHWC [n][64][80], through a shared-memory transpose
 __global__ void __launch_bounds__(256)
-planes_f16_to_nhwc_kernel(const __half* __restrict__ in, int n, __nv_bfloat16* __restrict__ out) {
+planes_f16_to_nhwc_kernel(const __half* __restrict__ in, int n, act_t* __restrict__ out) {
     __shared__ __half tile[74][64 + 2];
     const int p = blockIdx.x;
     if (p >= n) return;
@@ -157,8 +157,8 @@ planes_f16_to_nhwc_kernel(const __half* __restrict__ in, int n, __nv_bfloat16* _
             v[j] = c < 74 ? __half2float(tile[c][sq]) : 0.0f;
         }
         uint4 w;
-        w.x = pack_bf16x2(v[0], v[1]); w.y = pack_bf16x2(v[2], v[3]);
-        w.z = pack_bf16x2(v[4], v[5]); w.w = pack_bf16x2(v[6], v[7]);
+        w.x = pack_act2(v[0], v[1]); w.y = pack_act2(v[2], v[3]);
+        w.z = pack_act2(v[4], v[5]); w.w = pack_act2(v[6], v[7]);
         reinterpret_cast<uint4*>(out + (static_cast<size_t>(p) * 64 + sq) * PLANES_NHWC_C)[g] = w;
     }
 }
@@ -173,11 +173,11 @@ void launch_planes_nchw(const hm_packed_pos* pos, int n, void* out, int dtype, c
         default: planes_nchw_kernel<uint8_t><<<grid, PL_THREADS, 0, s>>>(pos, n, static_cast<uint8_t*>(out)); break;
     }
 }
-void launch_planes_nhwc(const hm_packed_pos* pos, int n, __nv_bfloat16* out, cudaStream_t s) {
+void launch_planes_nhwc(const hm_packed_pos* pos, int n, act_t* out, cudaStream_t s) {
     if (n <= 0) return;
     planes_nhwc_kernel<<<(n + PL_POS_PER_BLOCK - 1) / PL_POS_PER_BLOCK, PL_THREADS, 0, s>>>(pos, n, out);
 }
-void launch_planes_f16_to_nhwc(const __half* in, int n, __nv_bfloat16* out, cudaStream_t s) {
+void launch_planes_f16_to_nhwc(const __half* in, int n, act_t* out, cudaStream_t s) {
     if (n <= 0) return;
     planes_f16_to_nhwc_kernel<<<n, 256, 0, s>>>(in, n, out);
 }

@@ -1,0 +1,161 @@
+"""GPU parity, stage F and the fused path, through the C ABI.
+
+Tolerances (north_star): max |dvalue| <= 1e-2, policy KL(ref || ours) <= 1e-3 over the
+legal-move distribution, against the reference PyTorch fp32 forward (golden fixture produced by
+the reference model itself, tests/golden/forward_risev33.npz) and against the fp32 oracle."""
+import numpy as np
+import pytest
+
+from conftest import kl_divergence
+
+pytestmark = pytest.mark.gpu
+
+VALUE_TOL = 1e-2
+KL_TOL = 1e-3
+
+
+@pytest.fixture(scope="module")
+def blob():
+    from hivemind_b200 import weights as W
+
+    return W.random_hvmw(seed=0)
+
+
+@pytest.fixture(scope="module")
+def engine256(blob):
+    from hivemind_b200.engine import Engine
+
+    e = Engine(0, 256, 2)
+    assert e.loadNetworkFromMemory(blob)
+    yield e
+    e.close()
+
+
+def _max_kl(priors, ref_priors, offsets):
+    worst = 0.0
+    for i in range(len(offsets) - 1):
+        lo, hi = offsets[i], offsets[i + 1]
+        worst = max(worst, kl_divergence(ref_priors[lo:hi], priors[lo:hi]))
+    return worst
+
+
+def test_fused_path_matches_reference_model(engine256, gold_positions, gold_forward):
+    g, f = gold_positions, gold_forward
+    res = engine256.evaluatePositions(g["packed"], g["moves"], g["offsets"])
+    assert res is not None
+    priors, values, raw = res
+    assert np.abs(raw[:, 0] - f["value"]).max() <= VALUE_TOL
+    assert np.abs(raw[:, 4] - f["moves_left"]).max() <= VALUE_TOL
+    assert np.abs(raw[:, 1:4] - f["wdl"]).max() <= 5e-2       # raw logits, |wdl| up to ~4.5
+    assert _max_kl(priors, f["priors_f32"], g["offsets"]) <= KL_TOL
+    sums = np.add.reduceat(priors, g["offsets"][:-1].astype(np.int64))
+    assert np.allclose(sums, 1.0, atol=1e-5)
+
+
+def test_fused_values_are_shaped_raw_outputs(engine256, oracle, gold_positions):
+    g = gold_positions
+    priors, values, raw = engine256.evaluatePositions(g["packed"], g["moves"], g["offsets"])
+    want = np.array([oracle.shape_value(r[0], r[1:4], r[4]) for r in raw], np.float32)
+    assert np.allclose(values, want, atol=2e-7, rtol=0)
+
+
+def test_reference_shaped_half_path(engine256, oracle, gold_positions, gold_forward):
+    """enqueueInferenceHalf / synchronizeInferenceHalf with the reference's fp16 planes."""
+    from hivemind_b200.engine import HalfInferenceOutputs
+
+    g, f = gold_positions, gold_forward
+    obs = np.ascontiguousarray(g["planes_f16"]).view(np.float16)
+    out = HalfInferenceOutputs()
+    assert engine256.enqueueInferenceHalf(obs, 1)
+    assert not engine256.enqueueInferenceHalf(obs, 1)          # one request in flight per worker
+    assert engine256.synchronizeInferenceHalf(out, 1)
+    assert not engine256.synchronizeInferenceHalf(out, 1)      # sync without enqueue
+    assert out.value.shape == (256,) and out.policyA.shape == (256, 4672) and out.wdl.shape == (256, 3)
+    assert np.abs(out.value.astype(np.float32) - f["value"]).max() <= VALUE_TOL
+    assert np.abs(out.movesLeft.astype(np.float32) - f["moves_left"]).max() <= VALUE_TOL
+    # dense maps: index = ch*64+sq
+    assert np.abs(out.policyA[:8].astype(np.float32) - f["pi_a_first8"]).max() <= 0.15
+    assert np.abs(out.policyB[:8].astype(np.float32) - f["pi_b_first8"]).max() <= 0.15
+    # CPU-side decode exactly as the reference caller does it (utils.h:226-243) on OUR logits
+    pri = oracle.batch_priors_f16(out.policyA.view(np.uint16), out.policyB.view(np.uint16), g["packed"], g["moves"], g["offsets"])
+    assert _max_kl(pri, f["priors_f32"], g["offsets"]) <= KL_TOL
+
+
+def test_run_inference_float(engine256, gold_positions, gold_forward):
+    g, f = gold_positions, gold_forward
+    B = 256
+    obs = np.ascontiguousarray(g["planes_f32"])
+    value = np.zeros(B, np.float32); pa = np.zeros((B, 4672), np.float32); pb = np.zeros((B, 4672), np.float32)
+    wdl = np.zeros((B, 3), np.float32); ml = np.zeros(B, np.float32)
+    assert engine256.runInference(obs, value, pa, pb, wdl, ml, 0)
+    assert np.abs(value - f["value"]).max() <= VALUE_TOL
+    assert np.abs(pa[:8] - f["pi_a_first8"]).max() <= 0.15
+
+
+def test_short_and_ragged_batches(engine256, gold_positions, gold_forward):
+    g, f = gold_positions, gold_forward
+    for n in (1, 7, 130):
+        offs = g["offsets"][: 2 * n + 1]
+        res = engine256.evaluatePositions(g["packed"][:n], g["moves"][: offs[-1]], offs)
+        assert res is not None
+        priors, values, raw = res
+        assert np.abs(raw[:, 0] - f["value"][:n]).max() <= VALUE_TOL
+        assert _max_kl(priors, f["priors_f32"], offs) <= KL_TOL
+    # empty move lists are legal (nothing to normalise)
+    offs = np.zeros(2 * 4 + 1, np.uint32)
+    res = engine256.evaluatePositions(g["packed"][:4], np.zeros(0, np.uint32), offs)
+    assert res is not None and res[0].size == 0
+    # too many positions is refused, like an over-sized batch would be
+    from oracle.pyoracle import POS_DTYPE
+
+    assert engine256.evaluatePositions(np.zeros(257, POS_DTYPE), np.zeros(0, np.uint32), np.zeros(515, np.uint32)) is None
+
+
+def test_batch_invariance_and_determinism(engine256, gold_positions):
+    g = gold_positions
+    a = engine256.evaluatePositions(g["packed"], g["moves"], g["offsets"])
+    a = [x.copy() for x in a]
+    b = engine256.evaluatePositions(g["packed"], g["moves"], g["offsets"], 1)
+    assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    # a position's result does not depend on its slot or its neighbours
+    perm = np.arange(256)[::-1].copy()
+    pk = g["packed"][perm]
+    sizes = np.diff(g["offsets"].astype(np.int64)).reshape(256, 2)[perm].reshape(-1)
+    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint32)
+    mv = np.concatenate([g["moves"][g["offsets"][2 * p]: g["offsets"][2 * p + 2]] for p in perm])
+    c = engine256.evaluatePositions(pk, mv, offs)
+    assert np.array_equal(c[1], a[1][perm])
+    assert np.array_equal(c[2], a[2][perm])
+
+
+def test_full_size_batch512_properties(blob, gold_positions):
+    """BASELINE config 2 size: B = 512.  Size-independent properties: priors sum to 1, batch
+    halves agree with the 256-position run, values within [-1, 1]."""
+    from hivemind_b200.engine import Engine
+
+    g = gold_positions
+    e = Engine(0, 512, 1)
+    assert e.loadNetworkFromMemory(blob)
+    pk = np.concatenate([g["packed"], g["packed"]])
+    mv = np.concatenate([g["moves"], g["moves"]])
+    offs = np.concatenate([g["offsets"], g["offsets"][1:] + g["offsets"][-1]]).astype(np.uint32)
+    priors, values, raw = e.evaluatePositions(pk, mv, offs)
+    n = g["moves"].size
+    assert np.array_equal(priors[:n], priors[n:]) and np.array_equal(raw[:256], raw[256:])
+    assert (np.abs(values) <= 1.0).all()
+    sums = np.add.reduceat(priors, offs[:-1].astype(np.int64))
+    assert np.allclose(sums, 1.0, atol=1e-5)
+    e.close()
+
+
+def test_load_errors_return_false(tmp_path):
+    from hivemind_b200.engine import Engine, HalfInferenceOutputs
+
+    e = Engine(0, 8, 1)
+    assert not e.loadNetwork(str(tmp_path / "missing.onnx"), "")
+    bad = tmp_path / "bad.hvmw"
+    bad.write_bytes(b"not a weight file")
+    assert not e.loadNetwork(str(bad), "")
+    assert not e.enqueueInferenceHalf(np.zeros((8, 74, 8, 8), np.float16), 0)   # nothing loaded
+    assert not e.synchronizeInferenceHalf(HalfInferenceOutputs(), 0)
+    e.close()
