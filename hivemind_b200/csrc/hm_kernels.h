@@ -29,6 +29,9 @@ void launch_depthwise(const act_t* in, act_t* out, const float* w, const float* 
 // wt: [384 in][384 out] 16-bit (centre tap, transposed), b: [384] fp32.  in may equal out.
 void launch_eca(const act_t* in, act_t* out, const act_t* wt,
                 const float* b, int n, cudaStream_t s);
+// ECA gate only: gate[n][384] fp32 (the fused block kernel applies it)
+void launch_eca_gate(const act_t* in, const act_t* wt, const float* b, float* gate, int n,
+                     cudaStream_t s);
 // value head tail (builder_util.py:311-324): feat [n,64,16] 16-bit (after conv+BN+ReLU),
 // w4: [64 sq][16 c][4] fp32 (3 wdl rows + plys row, from Linear weights indexed c*64+sq),
 // b4: [4].  raw5: [n,5] fp32 {value, wdl_loss, wdl_draw, wdl_win, moves_left};

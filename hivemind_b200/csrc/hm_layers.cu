@@ -145,6 +145,49 @@ eca_kernel(const act_t* __restrict__ in, act_t* __restrict__ out,
     }
 }
 
+// Gate only (fused path): gate[pos][c] = hardsigmoid(Wc * mean_hw(x[pos]) + b) as fp32; the
+// scaling itself happens inside mbconv_kernel on the shared-memory input tile.
+constexpr int ECA_GP = 2;
+__global__ void __launch_bounds__(ECA_C)
+eca_gate_kernel(const act_t* __restrict__ in, const act_t* __restrict__ wt,
+                const float* __restrict__ bias, float* __restrict__ gate, int n) {
+    __shared__ float mean_s[ECA_GP][ECA_C];
+    const int p0 = blockIdx.x * ECA_GP;
+    const int np = min(ECA_GP, n - p0);
+    const int c = threadIdx.x;
+    for (int p = 0; p < np; ++p) {
+        const act_t* x = in + static_cast<size_t>(p0 + p) * 64 * ECA_C + c;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll 4
+        for (int sq = 0; sq < 64; sq += 4) {
+            s0 += act_to_float(x[static_cast<size_t>(sq) * ECA_C]);
+            s1 += act_to_float(x[static_cast<size_t>(sq + 1) * ECA_C]);
+            s2 += act_to_float(x[static_cast<size_t>(sq + 2) * ECA_C]);
+            s3 += act_to_float(x[static_cast<size_t>(sq + 3) * ECA_C]);
+        }
+        mean_s[p][c] = ((s0 + s1) + (s2 + s3)) * (1.0f / 64.0f);
+    }
+    for (int p = np; p < ECA_GP; ++p) mean_s[p][c] = 0.f;
+    __syncthreads();
+    float acc[ECA_GP];
+#pragma unroll
+    for (int p = 0; p < ECA_GP; ++p) acc[p] = 0.0f;
+#pragma unroll 8
+    for (int k = 0; k < ECA_C; ++k) {
+        const float wv = act_to_float(wt[static_cast<size_t>(k) * ECA_C + c]);
+#pragma unroll
+        for (int p = 0; p < ECA_GP; ++p) acc[p] = fmaf(wv, mean_s[p][k], acc[p]);
+    }
+    const float bv = bias[c];
+    for (int p = 0; p < np; ++p)
+        gate[static_cast<size_t>(p0 + p) * ECA_C + c] = fminf(fmaxf((acc[p] + bv) * (1.0f / 6.0f) + 0.5f, 0.0f), 1.0f);
+}
+void launch_eca_gate(const act_t* in, const act_t* wt, const float* b, float* gate, int n,
+                     cudaStream_t s) {
+    if (n <= 0) return;
+    eca_gate_kernel<<<(n + ECA_GP - 1) / ECA_GP, ECA_C, 0, s>>>(in, wt, b, gate, n);
+}
+
 void launch_eca(const act_t* in, act_t* out, const act_t* wt,
                 const float* b, int n, cudaStream_t s) {
     if (n <= 0) return;

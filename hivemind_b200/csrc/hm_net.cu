@@ -8,6 +8,7 @@
 #include <mutex>
 
 #include "hm_gemm.cuh"
+#include "hm_mbconv.cuh"
 #include "hm_kernels.h"
 
 namespace hm {
@@ -218,6 +219,39 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
             net->param_count += ew->numel() + eb->numel();
         }
         if (!blk.dw_w || !blk.dw_b) return nullptr;
+        {   // ---- fused-block layout (hm_mbconv.cuh) ----
+            const HvmwTensor *w1 = T(p + "pw1.w"), *b1 = T(p + "pw1.b"), *w2 = T(p + "pw2.w");
+            blk.cop_pad = round_up(blk.cop, 64);
+            const int cp = blk.cop_pad;
+            std::vector<act_t> w1p(static_cast<size_t>(cp) * 384, float_to_act(0.0f));
+            for (int o = 0; o < blk.cop; ++o)
+                for (int k = 0; k < 384; ++k) w1p[static_cast<size_t>(o) * 384 + k] = float_to_act(w1->data[static_cast<size_t>(o) * 384 + k]);
+            std::vector<act_t> w2p(static_cast<size_t>(384) * cp, float_to_act(0.0f));
+            for (int o = 0; o < 384; ++o)
+                for (int k = 0; k < blk.cop; ++k) w2p[static_cast<size_t>(o) * cp + k] = float_to_act(w2->data[static_cast<size_t>(o) * blk.cop + k]);
+            const int par_bytes = 384 + kk * 128;
+            blk.mb_par_stride = (par_bytes + 127) / 128 * 128;
+            std::vector<uint8_t> par(static_cast<size_t>(cp / 64) * blk.mb_par_stride, 0);
+            for (int ch = 0; ch < cp / 64; ++ch) {
+                uint8_t* base = par.data() + static_cast<size_t>(ch) * blk.mb_par_stride;
+                float* pb1 = reinterpret_cast<float*>(base);
+                act_t* pbd = reinterpret_cast<act_t*>(base + 256);
+                act_t* pw = reinterpret_cast<act_t*>(base + 384);
+                for (int j = 0; j < 64; ++j) {
+                    const int c = ch * 64 + j;
+                    const bool ok = c < blk.cop;
+                    pb1[j] = ok ? b1->data[c] : 0.0f;
+                    pbd[j] = float_to_act(ok ? db->data[c] : 0.0f);
+                    for (int t = 0; t < kk; ++t) pw[t * 64 + j] = float_to_act(ok ? dw->data[c * kk + t] : 0.0f);
+                }
+            }
+            blk.mb_w1 = upload(*net, w1p);
+            blk.mb_w2 = upload(*net, w2p);
+            blk.mb_par = upload(*net, par);
+            if (!blk.mb_w1 || !blk.mb_w2 || !blk.mb_par) return nullptr;
+            if (!make_tm_weights(&blk.tm_mw1, blk.mb_w1, cp, 384, 64)) return nullptr;
+            if (!make_tm_weights(&blk.tm_mw2, blk.mb_w2, 384, cp, 128)) return nullptr;
+        }
         net->blocks.push_back(blk);
     }
     if (net->blocks.empty()) { set_error("no residual blocks in blob"); return nullptr; }
@@ -296,7 +330,42 @@ static bool gemm_prepare() {
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL),
                  "cudaFuncSetAttribute(gemm)"))
         return false;
+    if (!cuda_ok(cudaFuncSetAttribute(mbconv_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, MbconvSmem<3>::TOTAL), "cudaFuncSetAttribute(mbconv3)") ||
+        !cuda_ok(cudaFuncSetAttribute(mbconv_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, MbconvSmem<5>::TOTAL), "cudaFuncSetAttribute(mbconv5)"))
+        return false;
     g_gemm_attr_set = true;
+    return true;
+}
+
+// One fused bottleneck block as an Op.
+static bool add_mbconv(std::vector<Op>& ops, const Block& b, int idx, const act_t* x, act_t* out,
+                       const float* gate, int n_pos, int num_sms) {
+    CUtensorMap tm_x;
+    if (!make_tm_act(&tm_x, x, n_pos, 384)) return false;
+    MbconvParams p{};
+    p.n_tiles = n_pos / 2;
+    p.n_chunks = b.cop_pad / 64;
+    p.par = b.mb_par;
+    p.par_stride = b.mb_par_stride;
+    p.bias2 = b.pw2.bias;
+    p.gate = gate;
+    p.x = x;
+    p.out = out;
+    const int grid = std::min(p.n_tiles, num_sms);
+    const CUtensorMap tw1 = b.tm_mw1, tw2 = b.tm_mw2;
+    const int ks = b.ksize;
+    Op op;
+    op.name = "b" + std::to_string(idx) + ".mbconv" + std::to_string(ks) + (gate ? "+eca" : "");
+    op.klass = "dense";
+    op.flops = 2.0 * (b.pw1.macs_per_pos() + b.pw2.macs_per_pos()) * n_pos;
+    op.bytes = 2.0 * n_pos * 64 * 384 * 2;
+    op.launch = [p, tm_x, tw1, tw2, grid, ks](cudaStream_t s) {
+        if (ks == 3)
+            mbconv_kernel<3><<<grid, MB_THREADS, MbconvSmem<3>::TOTAL, s>>>(p, tm_x, tw1, tw2);
+        else
+            mbconv_kernel<5><<<grid, MB_THREADS, MbconvSmem<5>::TOTAL, s>>>(p, tm_x, tw1, tw2);
+    };
+    ops.push_back(std::move(op));
     return true;
 }
 
@@ -362,7 +431,7 @@ static bool setup_worker(Engine* e, Worker& w) {
               dev_alloc(w, &w.d_trunk[1], rows * 384) && dev_alloc(w, &w.d_exp[0], rows * max_cop) &&
               dev_alloc(w, &w.d_exp[1], rows * max_cop) && dev_alloc(w, &w.d_pol_shared, rows * 384) &&
               dev_alloc(w, &w.d_logits, rows * POLICY_LD) && dev_alloc(w, &w.d_vfeat, rows * 16) &&
-              dev_alloc(w, &w.d_raw5, static_cast<size_t>(B) * 5) && dev_alloc(w, &w.d_value_h, B) &&
+              dev_alloc(w, &w.d_raw5, static_cast<size_t>(B) * 5) && dev_alloc(w, &w.d_gate, static_cast<size_t>(B) * 384) && dev_alloc(w, &w.d_value_h, B) &&
               dev_alloc(w, &w.d_wdl_h, static_cast<size_t>(B) * 3) && dev_alloc(w, &w.d_ml_h, B) &&
               dev_alloc(w, &w.d_pi_a, static_cast<size_t>(B) * HM_NB_POLICY_VALUES) &&
               dev_alloc(w, &w.d_pi_b, static_cast<size_t>(B) * HM_NB_POLICY_VALUES);
@@ -380,10 +449,33 @@ static bool setup_worker(Engine* e, Worker& w) {
     int cur = 0;
     if (!add_dense(ops, net.stem, w.d_planes, PLANES_NHWC_C, B, w.d_trunk[cur], 384, true, false, nullptr, 0)) return false;
     w.debug_views["stem"] = {w.d_trunk[cur], {static_cast<int>(rows), 384, 0}};
+    const char* unfused_env = getenv("HM_UNFUSED");
+    const bool fused = !(unfused_env && unfused_env[0] == '1');
+    int num_sms = 148;
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, e->device);
     for (size_t i = 0; i < net.blocks.size(); ++i) {
         const Block& b = net.blocks[i];
         act_t* x = w.d_trunk[cur];
         act_t* y = w.d_trunk[cur ^ 1];
+        if (fused) {
+            const float* gate = nullptr;
+            if (b.eca) {
+                Op op;
+                op.name = "b" + std::to_string(i) + ".eca_gate";
+                op.klass = "eca";
+                op.bytes = static_cast<double>(rows) * 384 * 2;
+                const act_t* wt = b.eca_wt;
+                const float* eb = b.eca_b;
+                float* g = w.d_gate;
+                op.launch = [x, wt, eb, g, B](cudaStream_t s) { launch_eca_gate(x, wt, eb, g, B, s); };
+                ops.push_back(std::move(op));
+                gate = w.d_gate;
+            }
+            if (!add_mbconv(ops, b, static_cast<int>(i), x, y, gate, B, num_sms)) return false;
+            cur ^= 1;
+            w.debug_views["block" + std::to_string(i)] = {w.d_trunk[cur], {static_cast<int>(rows), 384, 0}};
+            continue;
+        }
         if (b.eca) {
             Op op;
             op.name = "b" + std::to_string(i) + ".eca";

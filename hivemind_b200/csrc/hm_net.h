@@ -57,6 +57,13 @@ struct Block {
     float* dw_b = nullptr;  // [cop]
     act_t* eca_wt = nullptr;  // [384 in][384 out]
     float* eca_b = nullptr;
+    // fused-block (mbconv_kernel) parameter layout
+    int cop_pad = 0;          // cop rounded up to 64
+    act_t* mb_w1 = nullptr;   // [cop_pad][384]
+    act_t* mb_w2 = nullptr;   // [384][cop_pad]
+    uint8_t* mb_par = nullptr;  // per 64-channel chunk: bias1 f32[64] | dw bias half[64] | dw w half[taps][64]
+    int mb_par_stride = 0;
+    CUtensorMap tm_mw1, tm_mw2;
 };
 struct Net {
     int arch = HM_ARCH_RISEV33;
@@ -105,6 +112,7 @@ struct Worker {
     float* d_logits = nullptr;
     act_t* d_vfeat = nullptr;
     float* d_raw5 = nullptr;
+    float* d_gate = nullptr;
     __half *d_value_h = nullptr, *d_wdl_h = nullptr, *d_ml_h = nullptr, *d_pi_a = nullptr,
            *d_pi_b = nullptr;
     // pinned host mirrors (engine-owned outputs, engine.h:45-51)
