@@ -97,41 +97,60 @@ __device__ void mbconv_compute(const MbconvParams& p, uint8_t* smem, uint64_t* b
             named_bar_sync(1, MB_COMPUTE);  // Y complete
 
             // ---- depthwise k x k + bias + ReLU: Y -> Z[b] (A operand of pw2) ----
+            // Thread = (position, file x, 4-channel group): it owns the 8 squares of one file.
+            // Input rows slide through registers: every Y element is loaded once per kx and feeds
+            // up to KS outputs; rank validity is resolved at compile time, file validity by a
+            // select (no branches), so all loads of a row are in flight together.
             wait_empty(&bars[BAR_Z_EMPTY + b], z_n[b]);
             {
-                const int g = ct & 7;
-                const uint4 bd = *reinterpret_cast<const uint4*>(par + 256 + g * 16);
-                const uint8_t* wbase = par + 384 + g * 16;
-                uint8_t* zbuf = smem + S::Z_OFF + b * 16384;
+                const int cg = ct & 15, xcol = (ct >> 4) & 7, pbase = (ct >> 7) << 6;
+                const uint32_t sub = (cg & 1) * 8, unit = cg >> 1;
+                const uint2 bd = *reinterpret_cast<const uint2*>(par + 256 + cg * 8);
+                uint2 w[KS * KS];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int r = (ct >> 3) + 32 * i;
-                    const int pbase = r & 64, y = (r >> 3) & 7, x = r & 7;
-                    act2_t a0 = as_act2(bd.x), a1 = as_act2(bd.y), a2 = as_act2(bd.z), a3 = as_act2(bd.w);
+                for (int t = 0; t < KS * KS; ++t) w[t] = *reinterpret_cast<const uint2*>(par + 384 + t * 128 + cg * 8);
+                act2_t acc[8][2];
+#pragma unroll
+                for (int y = 0; y < 8; ++y) { acc[y][0] = as_act2(bd.x); acc[y][1] = as_act2(bd.y); }
+                uint32_t xoff[KS];
+                bool xok[KS];
+#pragma unroll
+                for (int kx = 0; kx < KS; ++kx) {
+                    const int xx = xcol + kx - H;
+                    xok[kx] = static_cast<unsigned>(xx) < 8u;
+                    const int xc = xok[kx] ? xx : xcol;
+                    // row & 7 == file, so the swizzle key is the (clamped) file
+                    xoff[kx] = static_cast<uint32_t>(xc) * 128u + ((unit ^ static_cast<uint32_t>(xc)) << 4) + sub;
+                }
+                const uint8_t* ybase = smem + S::Y_OFF + pbase * 128;
+#pragma unroll
+                for (int yy = 0; yy < 8; ++yy) {
+                    uint2 v[KS];
+#pragma unroll
+                    for (int kx = 0; kx < KS; ++kx) {
+                        v[kx] = *reinterpret_cast<const uint2*>(ybase + yy * 1024 + xoff[kx]);
+                        if (!xok[kx]) v[kx] = make_uint2(0u, 0u);
+                    }
 #pragma unroll
                     for (int ky = 0; ky < KS; ++ky) {
-                        const int yy = y + ky - H;
-                        if (yy < 0 || yy > 7) continue;
+                        const int y = yy - ky + H;
+                        if (y < 0 || y > 7) continue;  // compile-time after unrolling
 #pragma unroll
                         for (int kx = 0; kx < KS; ++kx) {
-                            const int xx = x + kx - H;
-                            if (xx < 0 || xx > 7) continue;
-                            const int nr = pbase + yy * 8 + xx;
-                            const uint4 v = *reinterpret_cast<const uint4*>(smem + S::Y_OFF + nr * 128 + ((g ^ (nr & 7)) << 4));
-                            const uint4 w = *reinterpret_cast<const uint4*>(wbase + (ky * KS + kx) * 128);
-                            a0 = __hfma2(as_act2(v.x), as_act2(w.x), a0);
-                            a1 = __hfma2(as_act2(v.y), as_act2(w.y), a1);
-                            a2 = __hfma2(as_act2(v.z), as_act2(w.z), a2);
-                            a3 = __hfma2(as_act2(v.w), as_act2(w.w), a3);
+                            acc[y][0] = __hfma2(as_act2(v[kx].x), as_act2(w[ky * KS + kx].x), acc[y][0]);
+                            acc[y][1] = __hfma2(as_act2(v[kx].y), as_act2(w[ky * KS + kx].y), acc[y][1]);
                         }
                     }
-                    const act2_t zero = as_act2(0u);
-                    uint4 o;
-                    o.x = as_u32(__hmax2(a0, zero));
-                    o.y = as_u32(__hmax2(a1, zero));
-                    o.z = as_u32(__hmax2(a2, zero));
-                    o.w = as_u32(__hmax2(a3, zero));
-                    *reinterpret_cast<uint4*>(zbuf + r * 128 + ((g ^ (r & 7)) << 4)) = o;
+                }
+                const act2_t zero = as_act2(0u);
+                uint8_t* zbuf = smem + S::Z_OFF + b * 16384 + pbase * 128;
+                const uint32_t zoff = static_cast<uint32_t>(xcol) * 128u + ((unit ^ static_cast<uint32_t>(xcol)) << 4) + sub;
+#pragma unroll
+                for (int y = 0; y < 8; ++y) {
+                    uint2 o;
+                    o.x = as_u32(__hmax2(acc[y][0], zero));
+                    o.y = as_u32(__hmax2(acc[y][1], zero));
+                    *reinterpret_cast<uint2*>(zbuf + y * 1024 + zoff) = o;
                 }
             }
             fence_proxy_async_smem();  // generic-proxy writes of Z -> visible to the tensor core
@@ -150,35 +169,39 @@ __device__ void mbconv_compute(const MbconvParams& p, uint8_t* smem, uint64_t* b
         if (has_gate && next < p.n_tiles) scale_x(next, tile_n + 1);
 
         // ---- final epilogue: D2 + bias2 + residual -> out ----
-        wait_full(&bars[BAR_D2_FULL], tile_n);
-        tc_fence_after();
         {
             const size_t grow = static_cast<size_t>(tile) * 128 + trow;
-            const act_t* xr = p.x + grow * MB_C;
-            act_t* orow = p.out + grow * MB_C;
-            const float* gs = gates + (tile_n & 1) * 2 * MB_C + (trow >> 6) * MB_C;
-#pragma unroll 1
-            for (int cc = 0; cc < 6; ++cc) {
-                const int col0 = colhalf * 192 + cc * 32;
-                uint32_t acc[32];
-                tmem_ld_32x32b_x32(tm_d2 + lane_off + col0, acc);
-                uint4 rv[4];
+            const act_t* xr = p.x + grow * MB_C + colhalf * 192;
+            act_t* orow = p.out + grow * MB_C + colhalf * 192;
+            const float* gs = gates + (tile_n & 1) * 2 * MB_C + (trow >> 6) * MB_C + colhalf * 192;
+            const float* b2 = b2s + colhalf * 192;
+            uint4 rv[2][4];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) rv[q] = __ldg(reinterpret_cast<const uint4*>(xr + col0) + q);
+            for (int q = 0; q < 4; ++q) rv[0][q] = __ldg(reinterpret_cast<const uint4*>(xr) + q);
+            wait_full(&bars[BAR_D2_FULL], tile_n);
+            tc_fence_after();
+#pragma unroll
+            for (int cc = 0; cc < 6; ++cc) {
+                const int col0 = cc * 32;
+                uint32_t acc[32];
+                tmem_ld_32x32b_x32(tm_d2 + lane_off + colhalf * 192 + col0, acc);
+                if (cc + 1 < 6) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) rv[(cc + 1) & 1][q] = __ldg(reinterpret_cast<const uint4*>(xr + col0 + 32) + q);
+                }
                 tmem_ld_wait();
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const uint32_t ru[4] = {rv[q].x, rv[q].y, rv[q].z, rv[q].w};
+                    const uint4 rq = rv[cc & 1][q];
+                    const uint32_t ru[4] = {rq.x, rq.y, rq.z, rq.w};
                     uint32_t ou[4];
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         const int j = q * 8 + e * 2;
                         float2 r = unpack_act2(ru[e]);
-                        if (has_gate) {
-                            r = unpack_act2(pack_act2(r.x * gs[col0 + j], r.y * gs[col0 + j + 1]));
-                        }
-                        ou[e] = pack_act2(__uint_as_float(acc[j]) + b2s[col0 + j] + r.x,
-                                          __uint_as_float(acc[j + 1]) + b2s[col0 + j + 1] + r.y);
+                        if (has_gate) r = unpack_act2(pack_act2(r.x * gs[col0 + j], r.y * gs[col0 + j + 1]));
+                        ou[e] = pack_act2(__uint_as_float(acc[j]) + b2[col0 + j] + r.x,
+                                          __uint_as_float(acc[j + 1]) + b2[col0 + j + 1] + r.y);
                     }
                     reinterpret_cast<uint4*>(orow + col0)[q] = make_uint4(ou[0], ou[1], ou[2], ou[3]);
                 }
