@@ -145,11 +145,18 @@ int hm_engine_enqueue_half(hm_engine* h, const uint16_t* obs, size_t worker) {
     if (w->pending) { set_error("worker already has a request in flight"); return 0; }  // engine.cc:584-588
     const size_t B = h->e.batch;
     cudaStream_t s = w->stream;
-    bool ok = cuda_ok(cudaMemcpyAsync(w->d_obs, obs, B * HM_NB_INPUT_VALUES * 2, cudaMemcpyHostToDevice, s), "H2D obs") &&
+    // the network's input layout IS the reference's obs layout (NCHW fp16): upload in place
+    static_assert(sizeof(act_t) == 2, "16-bit activations");
+#ifdef HM_ACT_BF16
+    set_error("the reference-shaped fp16 entry point needs the fp16 build");
+    return 0;
+#endif
+    const size_t prow = static_cast<size_t>(POLICY_CH) * 64 * 2, pw = static_cast<size_t>(HM_NB_POLICY_VALUES) * 2;
+    bool ok = cuda_ok(cudaMemcpyAsync(w->d_planes, obs, B * HM_NB_INPUT_VALUES * 2, cudaMemcpyHostToDevice, s), "H2D obs") &&
               cuda_ok(cudaGraphLaunch(w->graph_dense, s), "graph launch") &&
               cuda_ok(cudaMemcpyAsync(w->h_value, w->d_value_h, B * 2, cudaMemcpyDeviceToHost, s), "D2H value") &&
-              cuda_ok(cudaMemcpyAsync(w->h_pi_a, w->d_pi_a, B * HM_NB_POLICY_VALUES * 2, cudaMemcpyDeviceToHost, s), "D2H piA") &&
-              cuda_ok(cudaMemcpyAsync(w->h_pi_b, w->d_pi_b, B * HM_NB_POLICY_VALUES * 2, cudaMemcpyDeviceToHost, s), "D2H piB") &&
+              cuda_ok(cudaMemcpy2DAsync(w->h_pi_a, pw, w->d_pi, prow, pw, B, cudaMemcpyDeviceToHost, s), "D2H piA") &&
+              cuda_ok(cudaMemcpy2DAsync(w->h_pi_b, pw, w->d_pi + HM_NB_POLICY_VALUES, prow, pw, B, cudaMemcpyDeviceToHost, s), "D2H piB") &&
               cuda_ok(cudaMemcpyAsync(w->h_wdl, w->d_wdl_h, B * 3 * 2, cudaMemcpyDeviceToHost, s), "D2H wdl") &&
               cuda_ok(cudaMemcpyAsync(w->h_ml, w->d_ml_h, B * 2, cudaMemcpyDeviceToHost, s), "D2H ml");
     if (!ok) return 0;
@@ -403,10 +410,19 @@ int hm_engine_profile_pass(hm_engine* h, size_t worker, hm_kernel_time* out, int
         if (!cuda_ok(cudaEventCreate(&ev), "event")) return 0;
         w->events.push_back(ev);
     }
+    const bool checked = getenv("HM_CHECKED") != nullptr;  // bring-up aid: name the first failing launch
     cudaEventRecord(w->events[0], w->stream);
     for (size_t i = 0; i < ops.size(); ++i) {
         ops[i]->launch(w->stream);
         cudaEventRecord(w->events[i + 1], w->stream);
+        if (checked) {
+            cudaError_t err = cudaStreamSynchronize(w->stream);
+            if (err == cudaSuccess) err = cudaGetLastError();
+            if (err != cudaSuccess) {
+                set_error("launch '" + ops[i]->name + "' failed: " + cudaGetErrorString(err));
+                return 0;
+            }
+        }
     }
     if (!cuda_ok(cudaStreamSynchronize(w->stream), "profile sync")) return 0;
     if (!cuda_ok(cudaGetLastError(), "profile pass")) return 0;

@@ -1,0 +1,191 @@
+// hm_cgemm.cuh — tcgen05 + TMA implicit-GEMM convolution on NCHW activations, used for every
+// dense layer outside the residual trunk (stem 3x3, value 1x1,
+// policy 3x3 convs; reference builder_util.py:154-178, 246-326, rise_mobile_v3.py:38-57).
+//
+// Channel-major ("transposed") formulation: output channels are the MMA M dimension, board
+// squares the N dimension,
+//
+//   D[o, (pos, sq)] = act( sum_{tap, c} W[o, tap*Cpad + c] * X[pos, c, sq + shift(tap)] + bias[o] )
+//
+// A = W tile [128 out-channels x 64 K], K-major, 128-byte swizzle (TMA 2-D box).
+// B = activation block [2 positions][64 channels][64 squares], MN-major (squares contiguous),
+//     loaded by ONE 3-D TMA box (square, channel, position).  A vertical tap offset dy is a
+//     shift of the square coordinate by 8*dy: squares shifted off the board and channels beyond
+//     C are zero-filled by the TMA unit, so neither padding nor an im2col buffer exists.  (TMA
+//     cannot shift the innermost dimension by one element — 16-byte granularity — so the
+//     horizontal offset dx is NOT applied on the way in.)
+// D = for a 3x3 convolution THREE accumulators P_dx (128 channel lanes x 128 fp32 columns each),
+//     one per horizontal offset: P_dx[o,(y,x)] = sum_{dy,c} W[o;dy,dx;c] * X[c; y+dy, x].  The
+//     epilogue thread owns one output channel and whole board ranks in registers, so it finishes
+//     the convolution with out[y][x] = P_-1[y][x-1] + P_0[y][x] + P_+1[y][x+1] (zero beyond the
+//     files a/h) — a register shift.  Its 64 squares of a position are one contiguous 128-byte
+//     row of the NCHW output, written with 16-byte stores.
+//
+// CTA = (2 positions, 128 output channels); 192 threads: warp 0 TMA producer, warp 1 MMA
+// issuer + TMEM owner, warps 2-5 epilogue.
+#pragma once
+#include <cuda.h>
+#include "hm_ptx.cuh"
+
+namespace hm {
+
+struct CgemmParams {
+    int m_blocks;       // ceil(cout / 128)
+    int n_valid;        // cout: channels actually stored
+    int ksize;          // 1 or 3
+    int kblocks;        // Cpad / 64 per tap
+    const float* bias;  // [cout] or nullptr
+    void* out;          // [pos][out_channels][64], act_t or fp32
+    int out_channels;   // channel count of the output tensor
+    int relu;
+    int out_f32;
+};
+
+constexpr int CG_THREADS = 192;
+constexpr int CG_STAGES = 3;
+constexpr int CG_STAGE_BYTES = 32768;  // A 16 KB + B 16 KB
+constexpr int CG_SMEM = CG_STAGES * CG_STAGE_BYTES + 256 + 1024;
+
+__global__ void __launch_bounds__(CG_THREADS)
+cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
+             const __grid_constant__ CUtensorMap tmX) {
+    extern __shared__ uint8_t cg_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cg_smem_raw) + 1023) &
+                                               ~static_cast<uintptr_t>(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + CG_STAGES * CG_STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + CG_STAGES;
+    uint64_t* accum_bar = empty_bar + CG_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int tile = blockIdx.x / p.m_blocks;
+    const int mb = blockIdx.x - tile * p.m_blocks;
+    const int taps = p.ksize * p.ksize;
+    const int k_iters = taps * p.kblocks;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmW);
+        tma_prefetch_desc(&tmX);
+        for (int s = 0; s < CG_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(accum_bar, 1);
+        fence_barrier_init();
+    }
+    const uint32_t tmem_cols = p.ksize == 3 ? 512u : 128u;
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, tmem_cols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            const int half = p.ksize >> 1;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int it = 0; it < k_iters; ++it) {
+                const int tap = it / p.kblocks;
+                const int kb = it - tap * p.kblocks;
+                const int dy = tap / p.ksize - half;
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                uint8_t* a_dst = smem + stage * CG_STAGE_BYTES;
+                mbar_arrive_expect_tx(&full_bar[stage], CG_STAGE_BYTES);
+                tma_load_2d(a_dst, &tmW, &full_bar[stage], it * 64, mb * 128);
+                tma_load_3d(a_dst + 16384, &tmX, &full_bar[stage], 8 * dy, kb * 64, tile * 2);
+                if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int it = 0; it < k_iters; ++it) {
+                const int tap = it / p.kblocks;
+                const int acc_i = tap % p.ksize;              // horizontal offset dx + 1 (0 for 1x1)
+                const bool first = tap < p.ksize && it == tap * p.kblocks;  // first tile of this accumulator
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(smem + stage * CG_STAGE_BYTES);
+                const uint64_t a_desc = umma_desc_sw128(a_addr);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    // A: +32 B along K inside the swizzle row; B: +16 channel rows = 2 K groups
+                    const uint64_t b_desc = umma_desc_mn_sw128(a_addr + 16384 + k * 2048, 8192, 1024);
+                    umma_f16(tmem_base + acc_i * 128, a_desc + 2 * k, b_desc, idesc, (first && k == 0) ? 0u : 1u);
+                }
+                umma_commit(&empty_bar[stage]);
+                if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
+            }
+            umma_commit(accum_bar);
+        }
+    } else {
+        // ===== epilogue: thread = one output channel, both positions =====
+        const int q = warp & 3;
+        const int ch = mb * 128 + q * 32 + lane;
+        const bool valid = ch < p.n_valid;
+        const float bias = (valid && p.bias != nullptr) ? __ldg(p.bias + ch) : 0.0f;
+        mbar_wait(accum_bar, 0);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+        for (int c0 = 0; c0 < 128; c0 += 32) {
+            float v[32];
+            {
+                uint32_t acc[32];
+                tmem_ld_32x32b_x32(t_row + (p.ksize == 3 ? 128 : 0) + c0, acc);  // centre column (dx = 0)
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]) + bias;
+            }
+            if (p.ksize == 3) {  // CTA-uniform
+                uint32_t l[32], r[32];
+                tmem_ld_32x32b_x32(t_row + c0, l);        // P_-1
+                tmem_ld_32x32b_x32(t_row + 256 + c0, r);  // P_+1
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    if ((j & 7) != 0) v[j] += __uint_as_float(l[j - 1]);
+                    if ((j & 7) != 7) v[j] += __uint_as_float(r[j + 1]);
+                }
+            }
+            if (!valid) continue;
+            const int pos = tile * 2 + (c0 >> 6);
+            const size_t row = (static_cast<size_t>(pos) * p.out_channels + ch) * 64 + (c0 & 63);
+            if (p.relu) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+            }
+            if (p.out_f32) {
+                float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + row);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            } else {
+                uint4* o = reinterpret_cast<uint4*>(static_cast<act_t*>(p.out) + row);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint4 w;
+                    w.x = pack_act2(v[8 * j + 0], v[8 * j + 1]);
+                    w.y = pack_act2(v[8 * j + 2], v[8 * j + 3]);
+                    w.z = pack_act2(v[8 * j + 4], v[8 * j + 5]);
+                    w.w = pack_act2(v[8 * j + 6], v[8 * j + 7]);
+                    o[j] = w;
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, tmem_cols);
+    }
+}
+
+}  // namespace hm

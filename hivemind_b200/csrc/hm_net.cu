@@ -4,11 +4,13 @@
 // :246-326 value head; rise_mobile_v3.py:38-57 shared policy heads).
 #include "hm_net.h"
 
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
-#include "hm_gemm.cuh"
-#include "hm_mbconv.cuh"
+#include "hm_cgemm.cuh"
+#include "hm_trunk.cuh"
 #include "hm_kernels.h"
 
 namespace hm {
@@ -84,11 +86,11 @@ bool tensormap_init() {
     if (!g_encode) set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
     return g_encode != nullptr;
 }
-// W: bf16 [rows][kcols] K-major, box = 64 K-elements x box_rows rows, 128-byte swizzle.
-static bool make_tm_weights(CUtensorMap* tm, const void* w, int rows, int kcols, int box_rows) {
+// W: 16-bit [rows][kcols] K-major, box = 64 K-elements x 128 rows, 128-byte swizzle.
+static bool make_tm_weights(CUtensorMap* tm, const void* w, size_t rows, int kcols) {
     cuuint64_t dims[2] = {static_cast<cuuint64_t>(kcols), static_cast<cuuint64_t>(rows)};
     cuuint64_t strides[1] = {static_cast<cuuint64_t>(kcols) * 2};
-    cuuint32_t box[2] = {64, static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t box[2] = {64, 128};
     cuuint32_t es[2] = {1, 1};
     CUresult r = g_encode(tm, HM_TMA_DTYPE, 2, const_cast<void*>(w), dims, strides,
                           box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -96,18 +98,19 @@ static bool make_tm_weights(CUtensorMap* tm, const void* w, int rows, int kcols,
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(W) failed: " + std::to_string(r)); return false; }
     return true;
 }
-// A: bf16 NHWC activation [n][8][8][C] as a 4-D map (C, x, y, pos); box = 64 channels x 8 x 8 x
-// 2 positions = the 128-row GEMM tile.  Shifted boxes read zeros outside the board.
-static bool make_tm_act(CUtensorMap* tm, const void* x, int n, int C) {
-    cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), 8, 8, static_cast<cuuint64_t>(n)};
-    cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(C) * 16,
-                             static_cast<cuuint64_t>(C) * 128};
-    cuuint32_t box[4] = {64, 8, 8, 2};
-    cuuint32_t es[4] = {1, 1, 1, 1};
-    CUresult r = g_encode(tm, HM_TMA_DTYPE, 4, const_cast<void*>(x), dims, strides,
+// NCHW activation [n][C][64] as a 3-D map (square, channel, position); box = 64 squares x 64
+// channels x 2 positions = one MN-major B-operand block (also the trunk's tile load / store).
+// A box shifted by +-8 squares reads zeros off the board, one shifted beyond the last channel
+// reads zeros too (convolution padding and K padding for free).
+static bool make_tm_act3(CUtensorMap* tm, const void* x, int n, int C) {
+    cuuint64_t dims[3] = {64, static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(n)};
+    cuuint64_t strides[2] = {128, static_cast<cuuint64_t>(C) * 128};
+    cuuint32_t box[3] = {64, 64, 2};
+    cuuint32_t es[3] = {1, 1, 1};
+    CUresult r = g_encode(tm, HM_TMA_DTYPE, 3, const_cast<void*>(x), dims, strides,
                           box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(A) failed: " + std::to_string(r)); return false; }
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(act3) failed: " + std::to_string(r)); return false; }
     return true;
 }
 
@@ -125,12 +128,9 @@ static T* upload(Net& net, const std::vector<T>& host) {
 }
 static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
-constexpr int GEMM_BN = 128;
-constexpr int GEMM_STAGES = 3;
-
-// conv weight [cout][cin][k][k] fp32 (+ optional bias [cout]) -> bf16 [n_rows][k*k*cpad],
-// K index = tap*cpad + c with tap = ky*k + kx (cross-correlation: in[y+ky-k/2][x+kx-k/2]).
-// `row_offset`/`dst` let two convs share one padded matrix (policy projections A|B).
+// conv weight [cout][cin][k][k] fp32 -> 16-bit [n_rows][k*k*cpad], K index = tap*cpad + c with
+// tap = ky*k + kx (cross-correlation: in[y+ky-k/2][x+kx-k/2]).  `row_offset` lets two convs
+// share one padded matrix (policy projections A|B).
 static void pack_conv(std::vector<act_t>& dst, int ktot, int cpad, const float* w, int cout,
                       int cin, int k, int row_offset) {
     for (int o = 0; o < cout; ++o)
@@ -144,23 +144,20 @@ static bool finish_dense(Net& net, DenseLayer& L, const std::vector<act_t>& w,
     L.w = upload(net, w);
     if (!L.w) return false;
     if (bias) {
-        std::vector<float> b(L.n_valid, 0.0f);
-        std::copy(bias->begin(), bias->end(), b.begin());
-        L.bias = upload(net, b);
+        L.bias = upload(net, *bias);
         if (!L.bias) return false;
     }
-    return make_tm_weights(&L.tm_w, L.w, L.n_rows, L.ksize * L.ksize * L.cpad, GEMM_BN);
+    return make_tm_weights(&L.tm_w, L.w, L.n_rows, L.ksize * L.ksize * L.cpad);
 }
 static bool make_dense(Net& net, DenseLayer& L, const std::string& name, const HvmwTensor* w,
-                       const HvmwTensor* b, int cin_pad_to = 0) {
+                       const HvmwTensor* b) {
     if (!w || w->dims.size() < 2) { set_error("missing tensor " + name + ".w"); return false; }
     L.name = name;
     L.cout = w->dims[0];
     L.cin = w->dims[1];
     L.ksize = w->dims.size() == 4 ? w->dims[2] : 1;
-    L.cpad = round_up(cin_pad_to > 0 ? cin_pad_to : L.cin, 64);
-    L.n_rows = round_up(L.cout, GEMM_BN);
-    L.n_valid = round_up(L.cout, 8);
+    L.cpad = round_up(L.cin, 64);
+    L.n_rows = round_up(L.cout, 128);
     const int ktot = L.ksize * L.ksize * L.cpad;
     std::vector<act_t> packed(static_cast<size_t>(L.n_rows) * ktot, float_to_act(0.0f));
     pack_conv(packed, ktot, L.cpad, w->data, L.cout, L.cin, L.ksize, 0);
@@ -179,31 +176,52 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
         return nullptr;
     }
     auto T = [&](const std::string& n) { return blob.find(n); };
-    if (!make_dense(*net, net->stem, "stem", T("stem.w"), T("stem.b"), PLANES_NHWC_C)) return nullptr;
+    if (!make_dense(*net, net->stem, "stem", T("stem.w"), T("stem.b"))) return nullptr;
     net->channels = net->stem.cout;
     if (net->channels != 384) { set_error("trunk width must be 384"); return nullptr; }
+
+    // ---- residual trunk: all blocks concatenated by 128-channel chunk (hm_trunk.cuh) ----
+    std::vector<act_t> w1cat, w2cat;
+    std::vector<float> par, bias2;
     for (int i = 0;; ++i) {
         const std::string p = "b" + std::to_string(i) + ".";
-        if (!T(p + "pw1.w")) break;
+        const HvmwTensor *w1 = T(p + "pw1.w"), *b1 = T(p + "pw1.b"), *w2 = T(p + "pw2.w"),
+                         *b2 = T(p + "pw2.b"), *dw = T(p + "dw.w"), *db = T(p + "dw.b");
+        if (!w1) break;
+        if (!b1 || !w2 || !b2 || !dw || !db || dw->dims.size() != 3 || w1->dims.size() != 2 ||
+            w1->dims[1] != 384 || w2->dims[0] != 384) {
+            set_error("missing / malformed tensors of block " + p);
+            return nullptr;
+        }
         Block blk;
-        if (!make_dense(*net, blk.pw1, p + "pw1", T(p + "pw1.w"), T(p + "pw1.b"))) return nullptr;
-        if (!make_dense(*net, blk.pw2, p + "pw2", T(p + "pw2.w"), T(p + "pw2.b"))) return nullptr;
-        const HvmwTensor* dw = T(p + "dw.w");
-        const HvmwTensor* db = T(p + "dw.b");
-        if (!dw || !db || dw->dims.size() != 3) { set_error("missing " + p + "dw"); return nullptr; }
         blk.cop = dw->dims[0];
         blk.ksize = dw->dims[1];
-        if (blk.cop % 8 != 0 || blk.cop != blk.pw1.cout || (blk.ksize != 3 && blk.ksize != 5)) {
+        if (blk.cop != static_cast<int>(w1->dims[0]) || blk.cop != static_cast<int>(w2->dims[1]) ||
+            (blk.ksize != 3 && blk.ksize != 5)) {
             set_error("unsupported depthwise shape in " + p);
             return nullptr;
         }
         const int kk = blk.ksize * blk.ksize;
-        std::vector<float> dww(static_cast<size_t>(kk) * blk.cop);
-        for (int c = 0; c < blk.cop; ++c)
-            for (int t = 0; t < kk; ++t) dww[static_cast<size_t>(t) * blk.cop + c] = dw->data[c * kk + t];
-        blk.dw_w = upload(*net, dww);
-        blk.dw_b = upload(*net, std::vector<float>(db->data, db->data + blk.cop));
-        net->param_count += dw->numel() + db->numel();
+        blk.n_chunks = (blk.cop + 127) / 128;
+        blk.chunk0 = net->total_chunks;
+        blk.bias2_off = static_cast<int>(bias2.size());
+        net->total_chunks += blk.n_chunks;
+        w1cat.resize(static_cast<size_t>(net->total_chunks) * 128 * 384, float_to_act(0.0f));
+        w2cat.resize(static_cast<size_t>(net->total_chunks) * 384 * 128, float_to_act(0.0f));
+        par.resize(static_cast<size_t>(net->total_chunks) * 27 * 128, 0.0f);
+        for (int c = 0; c < blk.cop; ++c) {
+            const int g = blk.chunk0 + c / 128, r = c % 128;
+            for (int k = 0; k < 384; ++k)
+                w1cat[(static_cast<size_t>(g) * 128 + r) * 384 + k] = float_to_act(w1->data[static_cast<size_t>(c) * 384 + k]);
+            for (int o = 0; o < 384; ++o)
+                w2cat[(static_cast<size_t>(g) * 384 + o) * 128 + r] = float_to_act(w2->data[static_cast<size_t>(o) * blk.cop + c]);
+            float* pp = par.data() + static_cast<size_t>(g) * 27 * 128;
+            pp[r] = b1->data[c];
+            pp[128 + r] = db->data[c];
+            for (int t = 0; t < kk; ++t) pp[256 + t * 128 + r] = dw->data[c * kk + t];
+        }
+        bias2.insert(bias2.end(), b2->data, b2->data + 384);
+        net->param_count += w1->numel() + b1->numel() + w2->numel() + b2->numel() + dw->numel() + db->numel();
         if (const HvmwTensor* ew = T(p + "eca.w")) {
             const HvmwTensor* eb = T(p + "eca.b");
             if (!eb || ew->dims.size() != 2 || ew->dims[0] != 384 || ew->dims[1] != 384) {
@@ -216,45 +234,20 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
                 for (int k = 0; k < 384; ++k) wt[k * 384 + o] = float_to_act(ew->data[o * 384 + k]);
             blk.eca_wt = upload(*net, wt);
             blk.eca_b = upload(*net, std::vector<float>(eb->data, eb->data + 384));
+            if (!blk.eca_wt || !blk.eca_b) return nullptr;
             net->param_count += ew->numel() + eb->numel();
-        }
-        if (!blk.dw_w || !blk.dw_b) return nullptr;
-        {   // ---- fused-block layout (hm_mbconv.cuh) ----
-            const HvmwTensor *w1 = T(p + "pw1.w"), *b1 = T(p + "pw1.b"), *w2 = T(p + "pw2.w");
-            blk.cop_pad = round_up(blk.cop, 64);
-            const int cp = blk.cop_pad;
-            std::vector<act_t> w1p(static_cast<size_t>(cp) * 384, float_to_act(0.0f));
-            for (int o = 0; o < blk.cop; ++o)
-                for (int k = 0; k < 384; ++k) w1p[static_cast<size_t>(o) * 384 + k] = float_to_act(w1->data[static_cast<size_t>(o) * 384 + k]);
-            std::vector<act_t> w2p(static_cast<size_t>(384) * cp, float_to_act(0.0f));
-            for (int o = 0; o < 384; ++o)
-                for (int k = 0; k < blk.cop; ++k) w2p[static_cast<size_t>(o) * cp + k] = float_to_act(w2->data[static_cast<size_t>(o) * blk.cop + k]);
-            const int par_bytes = 384 + kk * 128;
-            blk.mb_par_stride = (par_bytes + 127) / 128 * 128;
-            std::vector<uint8_t> par(static_cast<size_t>(cp / 64) * blk.mb_par_stride, 0);
-            for (int ch = 0; ch < cp / 64; ++ch) {
-                uint8_t* base = par.data() + static_cast<size_t>(ch) * blk.mb_par_stride;
-                float* pb1 = reinterpret_cast<float*>(base);
-                act_t* pbd = reinterpret_cast<act_t*>(base + 256);
-                act_t* pw = reinterpret_cast<act_t*>(base + 384);
-                for (int j = 0; j < 64; ++j) {
-                    const int c = ch * 64 + j;
-                    const bool ok = c < blk.cop;
-                    pb1[j] = ok ? b1->data[c] : 0.0f;
-                    pbd[j] = float_to_act(ok ? db->data[c] : 0.0f);
-                    for (int t = 0; t < kk; ++t) pw[t * 64 + j] = float_to_act(ok ? dw->data[c * kk + t] : 0.0f);
-                }
-            }
-            blk.mb_w1 = upload(*net, w1p);
-            blk.mb_w2 = upload(*net, w2p);
-            blk.mb_par = upload(*net, par);
-            if (!blk.mb_w1 || !blk.mb_w2 || !blk.mb_par) return nullptr;
-            if (!make_tm_weights(&blk.tm_mw1, blk.mb_w1, cp, 384, 64)) return nullptr;
-            if (!make_tm_weights(&blk.tm_mw2, blk.mb_w2, 384, cp, 128)) return nullptr;
         }
         net->blocks.push_back(blk);
     }
     if (net->blocks.empty()) { set_error("no residual blocks in blob"); return nullptr; }
+    net->w1cat = upload(*net, w1cat);
+    net->w2cat = upload(*net, w2cat);
+    net->trunk_par = upload(*net, par);
+    net->trunk_bias2 = upload(*net, bias2);
+    if (!net->w1cat || !net->w2cat || !net->trunk_par || !net->trunk_bias2) return nullptr;
+    if (!make_tm_weights(&net->tm_w1, net->w1cat, static_cast<size_t>(net->total_chunks) * 128, 384)) return nullptr;
+    if (!make_tm_weights(&net->tm_w2, net->w2cat, static_cast<size_t>(net->total_chunks) * 384, 128)) return nullptr;
+
     // value head
     if (!make_dense(*net, net->value_conv, "value.conv", T("value.conv.w"), T("value.conv.b"))) return nullptr;
     {
@@ -264,19 +257,19 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
             set_error("value head tensors missing (WDL + plys configuration required)");
             return nullptr;
         }
-        std::vector<float> w4(64 * 16 * 4), b4(4);
-        for (int sq = 0; sq < 64; ++sq)
-            for (int c = 0; c < 16; ++c) {
-                for (int o = 0; o < 3; ++o) w4[(sq * 16 + c) * 4 + o] = ww->data[o * 1024 + c * 64 + sq];
-                w4[(sq * 16 + c) * 4 + 3] = pw->data[c * 64 + sq];
-            }
+        std::vector<float> w4(1024 * 4), b4(4);
+        for (int i = 0; i < 1024; ++i) {  // feature index i = c*64 + sq (builder_util.py:311 flatten)
+            for (int o = 0; o < 3; ++o) w4[i * 4 + o] = ww->data[o * 1024 + i];
+            w4[i * 4 + 3] = pw->data[i];
+        }
         for (int o = 0; o < 3; ++o) b4[o] = wb->data[o];
         b4[3] = pb->data[0];
         net->value_w4 = upload(*net, w4);
         net->value_b4 = upload(*net, b4);
+        if (!net->value_w4 || !net->value_b4) return nullptr;
         net->param_count += ww->numel() + wb->numel() + pw->numel() + pb->numel();
     }
-    // policy heads (shared trunk, two 73-channel projections packed side by side)
+    // policy heads (shared trunk, two 73-channel projections stacked)
     if (!make_dense(*net, net->policy_shared, "policy.shared", T("policy.shared.w"), T("policy.shared.b"))) return nullptr;
     {
         const HvmwTensor *pa = T("policy.a.w"), *pb = T("policy.b.w");
@@ -286,12 +279,11 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
         }
         DenseLayer& L = net->policy_proj;
         L.name = "policy.proj";
-        L.cout = 146;
+        L.cout = POLICY_CH;
         L.cin = pa->dims[1];
         L.ksize = pa->dims[2];
         L.cpad = round_up(L.cin, 64);
-        L.n_rows = round_up(POLICY_LD, GEMM_BN);
-        L.n_valid = POLICY_LD;
+        L.n_rows = round_up(POLICY_CH, 128);
         const int ktot = L.ksize * L.ksize * L.cpad;
         std::vector<act_t> packed(static_cast<size_t>(L.n_rows) * ktot, float_to_act(0.0f));
         pack_conv(packed, ktot, L.cpad, pa->data, 73, L.cin, L.ksize, 0);
@@ -322,83 +314,74 @@ static bool host_alloc(Worker& w, T** p, size_t count) {
     return true;
 }
 
-static bool g_gemm_attr_set = false;
-static bool gemm_prepare() {
-    if (g_gemm_attr_set) return true;
-    using S = GemmSmem<GEMM_BN, GEMM_STAGES>;
-    if (!cuda_ok(cudaFuncSetAttribute(gemm_tcgen05_kernel<GEMM_BN, GEMM_STAGES>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL),
-                 "cudaFuncSetAttribute(gemm)"))
-        return false;
-    if (!cuda_ok(cudaFuncSetAttribute(mbconv_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, MbconvSmem<3>::TOTAL), "cudaFuncSetAttribute(mbconv3)") ||
-        !cuda_ok(cudaFuncSetAttribute(mbconv_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, MbconvSmem<5>::TOTAL), "cudaFuncSetAttribute(mbconv5)"))
-        return false;
-    g_gemm_attr_set = true;
-    return true;
+static bool kernels_prepare() {
+    static std::once_flag once;
+    static bool ok = false;
+    std::call_once(once, []() {
+        ok = cuda_ok(cudaFuncSetAttribute(cgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CG_SMEM),
+                     "cudaFuncSetAttribute(cgemm)") &&
+             cuda_ok(cudaFuncSetAttribute(trunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM),
+                     "cudaFuncSetAttribute(trunk)");
+    });
+    return ok;
 }
 
-// One fused bottleneck block as an Op.
-static bool add_mbconv(std::vector<Op>& ops, const Block& b, int idx, const act_t* x, act_t* out,
-                       const float* gate, int n_pos, int num_sms) {
+// A run of consecutive bottleneck blocks [first, last) as one trunk_kernel launch.
+static bool add_trunk_run(std::vector<Op>& ops, const Net& net, int first, int last, act_t* x,
+                          const float* gate, float* sums, int n_pos) {
+    if (last - first > TR_MAX_BLOCKS) { set_error("trunk run too long"); return false; }
     CUtensorMap tm_x;
-    if (!make_tm_act(&tm_x, x, n_pos, 384)) return false;
-    MbconvParams p{};
-    p.n_tiles = n_pos / 2;
-    p.n_chunks = b.cop_pad / 64;
-    p.par = b.mb_par;
-    p.par_stride = b.mb_par_stride;
-    p.bias2 = b.pw2.bias;
+    if (!make_tm_act3(&tm_x, x, n_pos, 384)) return false;
+    TrunkParams p{};
+    p.n_blocks = last - first;
+    double macs = 0;
+    for (int i = first; i < last; ++i) {
+        const Block& b = net.blocks[i];
+        p.blk[i - first] = TrunkBlock{b.chunk0, b.n_chunks, b.ksize, b.bias2_off};
+        macs += b.macs_per_pos();
+    }
+    p.par = net.trunk_par;
+    p.bias2 = net.trunk_bias2;
     p.gate = gate;
-    p.x = x;
-    p.out = out;
-    const int grid = std::min(p.n_tiles, num_sms);
-    const CUtensorMap tw1 = b.tm_mw1, tw2 = b.tm_mw2;
-    const int ks = b.ksize;
+    p.sums = sums;
+    const int grid = n_pos / 2;
+    const CUtensorMap tw1 = net.tm_w1, tw2 = net.tm_w2;
     Op op;
-    op.name = "b" + std::to_string(idx) + ".mbconv" + std::to_string(ks) + (gate ? "+eca" : "");
+    op.name = "trunk.b" + std::to_string(first) + "-" + std::to_string(last - 1) + (gate ? "+eca" : "");
     op.klass = "dense";
-    op.flops = 2.0 * (b.pw1.macs_per_pos() + b.pw2.macs_per_pos()) * n_pos;
+    op.flops = 2.0 * macs * n_pos;
     op.bytes = 2.0 * n_pos * 64 * 384 * 2;
-    op.launch = [p, tm_x, tw1, tw2, grid, ks](cudaStream_t s) {
-        if (ks == 3)
-            mbconv_kernel<3><<<grid, MB_THREADS, MbconvSmem<3>::TOTAL, s>>>(p, tm_x, tw1, tw2);
-        else
-            mbconv_kernel<5><<<grid, MB_THREADS, MbconvSmem<5>::TOTAL, s>>>(p, tm_x, tw1, tw2);
+    op.launch = [p, tm_x, tw1, tw2, grid](cudaStream_t s) {
+        trunk_kernel<<<grid, TR_THREADS, TR_SMEM, s>>>(p, tm_x, tw1, tw2);
     };
     ops.push_back(std::move(op));
     return true;
 }
 
-// One dense layer as an Op: in = NHWC bf16 [n][64][cin_buf] -> out [n*64][ldc].
-static bool add_dense(std::vector<Op>& ops, const DenseLayer& L, const act_t* in,
-                      int cin_buf, int n_pos, void* out, int ldc, bool relu, bool out_f32,
-                      const act_t* residual, int ldr) {
-    CUtensorMap tm_a;
-    if (!make_tm_act(&tm_a, in, n_pos, cin_buf)) return false;
-    GemmParams p{};
-    p.M = n_pos * 64;
-    p.n_valid = L.n_valid;
+// One convolution as an Op: in = NCHW [n][cin_buf][64] -> out [n][out_channels][64].
+static bool add_dense(std::vector<Op>& ops, const DenseLayer& L, const act_t* in, int cin_buf,
+                      int n_pos, void* out, bool relu, bool out_f32, const char* suffix = "") {
+    CUtensorMap tm_x;
+    if (!make_tm_act3(&tm_x, in, n_pos, cin_buf)) return false;
+    CgemmParams p{};
+    p.m_blocks = L.n_rows / 128;
+    p.n_valid = L.cout;
     p.ksize = L.ksize;
-    p.kchunks = L.cpad / 64;
+    p.kblocks = L.cpad / 64;
     p.bias = L.bias;
-    p.residual = residual;
-    p.ldr = ldr;
     p.out = out;
-    p.ldc = ldc;
+    p.out_channels = L.cout;
     p.relu = relu ? 1 : 0;
     p.out_f32 = out_f32 ? 1 : 0;
-    p.chan_sum = nullptr;
-    const int n_tiles = (L.n_valid + GEMM_BN - 1) / GEMM_BN;
-    const int grid = (p.M / GEMM_BM) * n_tiles;
+    const int grid = (n_pos / 2) * p.m_blocks;
     const CUtensorMap tm_w = L.tm_w;
     Op op;
-    op.name = L.name;
+    op.name = L.name + suffix;
     op.klass = "dense";
     op.flops = 2.0 * L.macs_per_pos() * n_pos;
     op.bytes = 0;
-    op.launch = [p, tm_a, tm_w, grid](cudaStream_t s) {
-        gemm_tcgen05_kernel<GEMM_BN, GEMM_STAGES>
-            <<<grid, GEMM_THREADS, GemmSmem<GEMM_BN, GEMM_STAGES>::TOTAL, s>>>(p, tm_a, tm_w);
+    op.launch = [p, tm_w, tm_x, grid](cudaStream_t s) {
+        cgemm_kernel<<<grid, CG_THREADS, CG_SMEM, s>>>(p, tm_w, tm_x);
     };
     ops.push_back(std::move(op));
     return true;
@@ -419,101 +402,65 @@ static bool capture_graph(Worker& w, const std::vector<const std::vector<Op>*>& 
 static bool setup_worker(Engine* e, Worker& w) {
     const Net& net = *e->net;
     const int B = w.batch;
-    const size_t rows = static_cast<size_t>(B) * 64;
-    int max_cop = 0;
-    for (const Block& b : net.blocks) max_cop = std::max(max_cop, b.cop);
-    w.move_cap = static_cast<size_t>(B) * 2 * 256;
+    const size_t nb = static_cast<size_t>(B);
+    w.move_cap = nb * 2 * 256;
     if (!cuda_ok(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
-    bool ok = dev_alloc(w, &w.d_pos, B) && dev_alloc(w, &w.d_moves, w.move_cap) &&
-              dev_alloc(w, &w.d_offsets, 2 * B + 1) && dev_alloc(w, &w.d_priors, w.move_cap) &&
-              dev_alloc(w, &w.d_values, B) && dev_alloc(w, &w.d_obs, static_cast<size_t>(B) * HM_NB_INPUT_VALUES) &&
-              dev_alloc(w, &w.d_planes, rows * PLANES_NHWC_C) && dev_alloc(w, &w.d_trunk[0], rows * 384) &&
-              dev_alloc(w, &w.d_trunk[1], rows * 384) && dev_alloc(w, &w.d_exp[0], rows * max_cop) &&
-              dev_alloc(w, &w.d_exp[1], rows * max_cop) && dev_alloc(w, &w.d_pol_shared, rows * 384) &&
-              dev_alloc(w, &w.d_logits, rows * POLICY_LD) && dev_alloc(w, &w.d_vfeat, rows * 16) &&
-              dev_alloc(w, &w.d_raw5, static_cast<size_t>(B) * 5) && dev_alloc(w, &w.d_gate, static_cast<size_t>(B) * 384) && dev_alloc(w, &w.d_value_h, B) &&
-              dev_alloc(w, &w.d_wdl_h, static_cast<size_t>(B) * 3) && dev_alloc(w, &w.d_ml_h, B) &&
-              dev_alloc(w, &w.d_pi_a, static_cast<size_t>(B) * HM_NB_POLICY_VALUES) &&
-              dev_alloc(w, &w.d_pi_b, static_cast<size_t>(B) * HM_NB_POLICY_VALUES);
-    ok = ok && host_alloc(w, &w.h_pos, B) && host_alloc(w, &w.h_moves, w.move_cap) &&
-         host_alloc(w, &w.h_offsets, 2 * B + 1) && host_alloc(w, &w.h_priors, w.move_cap) &&
-         host_alloc(w, &w.h_values, B) && host_alloc(w, &w.h_raw5, static_cast<size_t>(B) * 5) &&
-         host_alloc(w, &w.h_obs, static_cast<size_t>(B) * HM_NB_INPUT_VALUES) &&
-         host_alloc(w, &w.h_value, B) && host_alloc(w, &w.h_wdl, static_cast<size_t>(B) * 3) &&
-         host_alloc(w, &w.h_ml, B) && host_alloc(w, &w.h_pi_a, static_cast<size_t>(B) * HM_NB_POLICY_VALUES) &&
-         host_alloc(w, &w.h_pi_b, static_cast<size_t>(B) * HM_NB_POLICY_VALUES);
-    if (!ok || !gemm_prepare()) return false;
+    bool ok = dev_alloc(w, &w.d_pos, nb) && dev_alloc(w, &w.d_moves, w.move_cap) &&
+              dev_alloc(w, &w.d_offsets, 2 * nb + 1) && dev_alloc(w, &w.d_priors, w.move_cap) &&
+              dev_alloc(w, &w.d_values, nb) && dev_alloc(w, &w.d_planes, nb * HM_NB_INPUT_VALUES) &&
+              dev_alloc(w, &w.d_trunk, nb * 384 * 64) && dev_alloc(w, &w.d_pol_shared, nb * 384 * 64) &&
+              dev_alloc(w, &w.d_logits, nb * POLICY_CH * 64) && dev_alloc(w, &w.d_pi, nb * POLICY_CH * 64) &&
+              dev_alloc(w, &w.d_vfeat, nb * 16 * 64) && dev_alloc(w, &w.d_raw5, nb * 5) &&
+              dev_alloc(w, &w.d_sums, nb * 384) && dev_alloc(w, &w.d_gate, nb * 384) &&
+              dev_alloc(w, &w.d_value_h, nb) && dev_alloc(w, &w.d_wdl_h, nb * 3) && dev_alloc(w, &w.d_ml_h, nb);
+    ok = ok && host_alloc(w, &w.h_pos, nb) && host_alloc(w, &w.h_moves, w.move_cap) &&
+         host_alloc(w, &w.h_offsets, 2 * nb + 1) && host_alloc(w, &w.h_priors, w.move_cap) &&
+         host_alloc(w, &w.h_values, nb) && host_alloc(w, &w.h_raw5, nb * 5) &&
+         host_alloc(w, &w.h_obs, nb * HM_NB_INPUT_VALUES) && host_alloc(w, &w.h_value, nb) &&
+         host_alloc(w, &w.h_wdl, nb * 3) && host_alloc(w, &w.h_ml, nb) &&
+         host_alloc(w, &w.h_pi_a, nb * HM_NB_POLICY_VALUES) && host_alloc(w, &w.h_pi_b, nb * HM_NB_POLICY_VALUES);
+    if (!ok || !kernels_prepare()) return false;
 
-    // ---- trunk: stem + blocks + heads ---------------------------------------------------
+    // ---- stem + residual trunk + value head + shared policy conv -----------------------------
     auto& ops = w.ops_trunk;
-    int cur = 0;
-    if (!add_dense(ops, net.stem, w.d_planes, PLANES_NHWC_C, B, w.d_trunk[cur], 384, true, false, nullptr, 0)) return false;
-    w.debug_views["stem"] = {w.d_trunk[cur], {static_cast<int>(rows), 384, 0}};
-    const char* unfused_env = getenv("HM_UNFUSED");
-    const bool fused = !(unfused_env && unfused_env[0] == '1');
-    int num_sms = 148;
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, e->device);
-    for (size_t i = 0; i < net.blocks.size(); ++i) {
-        const Block& b = net.blocks[i];
-        act_t* x = w.d_trunk[cur];
-        act_t* y = w.d_trunk[cur ^ 1];
-        if (fused) {
-            const float* gate = nullptr;
-            if (b.eca) {
-                Op op;
-                op.name = "b" + std::to_string(i) + ".eca_gate";
-                op.klass = "eca";
-                op.bytes = static_cast<double>(rows) * 384 * 2;
-                const act_t* wt = b.eca_wt;
-                const float* eb = b.eca_b;
-                float* g = w.d_gate;
-                op.launch = [x, wt, eb, g, B](cudaStream_t s) { launch_eca_gate(x, wt, eb, g, B, s); };
-                ops.push_back(std::move(op));
-                gate = w.d_gate;
-            }
-            if (!add_mbconv(ops, b, static_cast<int>(i), x, y, gate, B, num_sms)) return false;
-            cur ^= 1;
-            w.debug_views["block" + std::to_string(i)] = {w.d_trunk[cur], {static_cast<int>(rows), 384, 0}};
-            continue;
-        }
-        if (b.eca) {
+    if (!add_dense(ops, net.stem, w.d_planes, HM_NB_INPUT_CHANNELS, B, w.d_trunk, true, false)) return false;
+    int nblk = static_cast<int>(net.blocks.size());
+    if (const char* stop = getenv("HM_TRUNK_STOP"))  // debugging aid (tools/diagnose.py): truncate the trunk
+        nblk = std::max(0, std::min(nblk, atoi(stop)));
+    // runs of blocks are cut where an ECA gate needs the complete previous output
+    // (builder_util.py:77-80: the gate is a function of ALL channel means of the block input)
+    for (int first = 0; first < nblk;) {
+        int last = first + 1;
+        while (last < nblk && !net.blocks[last].eca && last - first < TR_MAX_BLOCKS) ++last;
+        const Block& b0 = net.blocks[first];
+        const float* gate = nullptr;
+        if (b0.eca) {
+            if (first == 0) { set_error("ECA on the first block is not supported"); return false; }
             Op op;
-            op.name = "b" + std::to_string(i) + ".eca";
+            op.name = "b" + std::to_string(first) + ".eca_gate";
             op.klass = "eca";
-            op.bytes = 2.0 * rows * 384 * 2;
-            const act_t* wt = b.eca_wt;
-            const float* eb = b.eca_b;
-            op.launch = [x, wt, eb, B](cudaStream_t s) { launch_eca(x, x, wt, eb, B, s); };
+            op.bytes = static_cast<double>(B) * 384 * 8;
+            const float* sums = w.d_sums;
+            const act_t* wt = b0.eca_wt;
+            const float* eb = b0.eca_b;
+            float* g = w.d_gate;
+            op.launch = [sums, wt, eb, g, B](cudaStream_t s) { launch_eca_gate(sums, wt, eb, g, B, s); };
             ops.push_back(std::move(op));
+            gate = w.d_gate;
         }
-        if (!add_dense(ops, b.pw1, x, 384, B, w.d_exp[0], b.cop, true, false, nullptr, 0)) return false;
-        {
-            Op op;
-            op.name = "b" + std::to_string(i) + ".dw" + std::to_string(b.ksize);
-            op.klass = "depthwise";
-            op.bytes = 2.0 * rows * b.cop * 2;
-            const act_t* in = w.d_exp[0];
-            act_t* out = w.d_exp[1];
-            const float *dw = b.dw_w, *db = b.dw_b;
-            const int cop = b.cop, ks = b.ksize;
-            op.launch = [in, out, dw, db, B, cop, ks](cudaStream_t s) { launch_depthwise(in, out, dw, db, B, cop, ks, s); };
-            ops.push_back(std::move(op));
-        }
-        if (!add_dense(ops, b.pw2, w.d_exp[1], b.cop, B, y, 384, false, false, x, 384)) return false;
-        cur ^= 1;
-        w.debug_views["block" + std::to_string(i)] = {w.d_trunk[cur], {static_cast<int>(rows), 384, 0}};
+        float* sums = (last < nblk && net.blocks[last].eca) ? w.d_sums : nullptr;
+        if (!add_trunk_run(ops, net, first, last, w.d_trunk, gate, sums, B)) return false;
+        first = last;
     }
-    // NOTE: trunk buffers ping-pong, so only the LAST writer of each buffer is inspectable
-    // after a pass; "trunk" is the final activation.
-    act_t* trunk = w.d_trunk[cur];
-    w.debug_views["trunk"] = {trunk, {static_cast<int>(rows), 384, 0}};
-    if (!add_dense(ops, net.value_conv, trunk, 384, B, w.d_vfeat, 16, true, false, nullptr, 0)) return false;
-    w.debug_views["value_feat"] = {w.d_vfeat, {static_cast<int>(rows), 16, 0}};
+    w.debug_views["planes"] = {w.d_planes, {B, HM_NB_INPUT_VALUES, 0}};
+    w.debug_views["trunk"] = {w.d_trunk, {B, 384 * 64, 0}};
+    if (!add_dense(ops, net.value_conv, w.d_trunk, 384, B, w.d_vfeat, true, false)) return false;
+    w.debug_views["value_feat"] = {w.d_vfeat, {B, 16 * 64, 0}};
     {
         Op op;
         op.name = "value.tail";
         op.klass = "head";
-        op.bytes = static_cast<double>(rows) * 16 * 2;
+        op.bytes = static_cast<double>(B) * 1024 * 2;
         const act_t* f = w.d_vfeat;
         const float *w4 = net.value_w4, *b4 = net.value_b4;
         float* raw5 = w.d_raw5;
@@ -521,46 +468,29 @@ static bool setup_worker(Engine* e, Worker& w) {
         op.launch = [f, w4, b4, B, raw5, vh, wh, mh](cudaStream_t s) { launch_value_tail(f, w4, b4, B, raw5, vh, wh, mh, s); };
         ops.push_back(std::move(op));
     }
-    if (!add_dense(ops, net.policy_shared, trunk, 384, B, w.d_pol_shared, 384, true, false, nullptr, 0)) return false;
-    w.debug_views["policy_shared"] = {w.d_pol_shared, {static_cast<int>(rows), 384, 0}};
-    if (!add_dense(ops, net.policy_proj, w.d_pol_shared, 384, B, w.d_logits, POLICY_LD, false, true, nullptr, 0)) return false;
-    w.debug_views["logits"] = {w.d_logits, {static_cast<int>(rows), POLICY_LD, 1}};
-    w.debug_views["planes"] = {w.d_planes, {static_cast<int>(rows), PLANES_NHWC_C, 0}};
-    w.debug_views["exp_pw1"] = {w.d_exp[0], {static_cast<int>(rows), net.blocks.back().cop, 0}};
-    w.debug_views["exp_dw"] = {w.d_exp[1], {static_cast<int>(rows), net.blocks.back().cop, 0}};
+    if (!add_dense(ops, net.policy_shared, w.d_trunk, 384, B, w.d_pol_shared, true, false)) return false;
+    w.debug_views["policy_shared"] = {w.d_pol_shared, {B, 384 * 64, 0}};
+    w.debug_views["logits"] = {w.d_logits, {B, POLICY_CH * 64, 1}};
 
-    // ---- reference-shaped pre/post ----------------------------------------------------------
-    {
-        Op op;
-        op.name = "planes.f16_to_nhwc";
-        op.klass = "planes";
-        op.bytes = static_cast<double>(B) * (HM_NB_INPUT_VALUES * 2 + 64 * PLANES_NHWC_C * 2);
-        const __half* in = w.d_obs;
-        act_t* out = w.d_planes;
-        op.launch = [in, out, B](cudaStream_t s) { launch_planes_f16_to_nhwc(in, B, out, s); };
-        w.ops_dense_in.push_back(std::move(op));
-    }
-    {
-        Op op;
-        op.name = "policy.dense_half";
-        op.klass = "policy";
-        op.bytes = static_cast<double>(rows) * POLICY_LD * 4 + 2.0 * B * HM_NB_POLICY_VALUES * 2;
-        const float* lg = w.d_logits;
-        __half *pa = w.d_pi_a, *pb = w.d_pi_b;
-        op.launch = [lg, B, pa, pb](cudaStream_t s) { launch_policy_dense_half(lg, B, pa, pb, s); };
-        w.ops_dense_out.push_back(std::move(op));
-    }
+    // ---- reference-shaped post: dense fp16 policy maps, index ch*64+sq (rise_mobile_v3.py:55) ----
+    if (!add_dense(w.ops_dense_out, net.policy_proj, w.d_pol_shared, 384, B, w.d_pi, false, false, ".f16")) return false;
     // ---- fused pre/post ---------------------------------------------------------------------
     {
         Op op;
-        op.name = "planes.encode_nhwc";
+        op.name = "planes.encode";
         op.klass = "planes";
-        op.bytes = static_cast<double>(B) * (256 + 64 * PLANES_NHWC_C * 2);
+        op.bytes = static_cast<double>(B) * (256 + HM_NB_INPUT_VALUES * 2);
         const hm_packed_pos* pp = w.d_pos;
         act_t* out = w.d_planes;
-        op.launch = [pp, out, B](cudaStream_t s) { launch_planes_nhwc(pp, B, out, s); };
+#ifdef HM_ACT_BF16
+        const int dt = HM_DTYPE_BF16;
+#else
+        const int dt = HM_DTYPE_F16;
+#endif
+        op.launch = [pp, out, B, dt](cudaStream_t s) { launch_planes_nchw(pp, B, out, dt, s); };
         w.ops_fused_in.push_back(std::move(op));
     }
+    if (!add_dense(w.ops_fused_out, net.policy_proj, w.d_pol_shared, 384, B, w.d_logits, false, true)) return false;
     {
         Op op;
         op.name = "policy.priors";
@@ -570,7 +500,7 @@ static bool setup_worker(Engine* e, Worker& w) {
         const hm_packed_pos* pp = w.d_pos;
         const uint32_t *mv = w.d_moves, *off = w.d_offsets;
         float* pri = w.d_priors;
-        op.launch = [lg, pp, B, mv, off, pri](cudaStream_t s) { launch_policy_priors_nhwc(lg, pp, B, mv, off, pri, s); };
+        op.launch = [lg, pp, B, mv, off, pri](cudaStream_t s) { launch_policy_priors_packed(lg, pp, B, mv, off, pri, s); };
         w.ops_fused_out.push_back(std::move(op));
         Op ov;
         ov.name = "value.shape";

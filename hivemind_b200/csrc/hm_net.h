@@ -38,43 +38,42 @@ struct HvmwBlob {
 };
 
 // ---- device-resident network parameters ----------------------------------------------------
-struct DenseLayer {            // one tcgen05 GEMM layer (1x1 or kxk convolution)
+struct DenseLayer {            // one tcgen05 implicit-GEMM convolution (hm_cgemm.cuh)
     std::string name;
     int cin = 0, cout = 0, ksize = 1;
     int cpad = 0;              // cin rounded up to 64 (K columns per tap)
     int n_rows = 0;            // cout rounded up to 128 (rows of the padded W)
-    int n_valid = 0;           // columns stored by the epilogue (multiple of 8)
-    act_t* w = nullptr;  // [n_rows][taps*cpad]
-    float* bias = nullptr;       // [n_valid] or null
+    act_t* w = nullptr;        // [n_rows][taps*cpad], K-major
+    float* bias = nullptr;     // [cout] or null
     CUtensorMap tm_w;
     double macs_per_pos() const { return 64.0 * cin * cout * ksize * ksize; }
 };
-struct Block {
+struct Block {                 // one bottleneck block inside the trunk kernel (hm_trunk.cuh)
     int cop = 0, ksize = 3;
     bool eca = false;
-    DenseLayer pw1, pw2;
-    float* dw_w = nullptr;  // [k*k][cop]
-    float* dw_b = nullptr;  // [cop]
-    act_t* eca_wt = nullptr;  // [384 in][384 out]
+    int chunk0 = 0, n_chunks = 0;  // 128-channel chunks in W1cat / W2cat / par
+    int bias2_off = 0;             // offset into Net::trunk_bias2
+    act_t* eca_wt = nullptr;       // [384 in][384 out]
     float* eca_b = nullptr;
-    // fused-block (mbconv_kernel) parameter layout
-    int cop_pad = 0;          // cop rounded up to 64
-    act_t* mb_w1 = nullptr;   // [cop_pad][384]
-    act_t* mb_w2 = nullptr;   // [384][cop_pad]
-    uint8_t* mb_par = nullptr;  // per 64-channel chunk: bias1 f32[64] | dw bias half[64] | dw w half[taps][64]
-    int mb_par_stride = 0;
-    CUtensorMap tm_mw1, tm_mw2;
+    double macs_per_pos() const { return 2.0 * 64.0 * 384.0 * cop; }
 };
 struct Net {
     int arch = HM_ARCH_RISEV33;
     int channels = 384;
     DenseLayer stem;
     std::vector<Block> blocks;
+    // trunk parameters, all blocks concatenated by 128-channel chunk
+    act_t* w1cat = nullptr;       // [chunks*128][384]
+    act_t* w2cat = nullptr;       // [chunks*384][128]
+    float* trunk_par = nullptr;   // [chunks][27*128]: pw1 bias | dw bias | 25 dw taps
+    float* trunk_bias2 = nullptr; // [blocks][384]
+    int total_chunks = 0;
+    CUtensorMap tm_w1, tm_w2;
     DenseLayer value_conv;       // 384 -> 16
-    float* value_w4 = nullptr;   // [64][16][4]
+    float* value_w4 = nullptr;   // [1024][4]
     float* value_b4 = nullptr;   // [4]
     DenseLayer policy_shared;    // 3x3 384 -> 384
-    DenseLayer policy_proj;      // 3x3 384 -> 146 (A: 0..72, B: 73..145), padded to 160
+    DenseLayer policy_proj;      // 3x3 384 -> 146 (A: 0..72, B: 73..145)
     std::vector<void*> allocations;
     size_t param_count = 0;
     ~Net();
@@ -104,17 +103,16 @@ struct Worker {
     uint32_t* d_offsets = nullptr;
     float* d_priors = nullptr;
     float* d_values = nullptr;
-    __half* d_obs = nullptr;
-    act_t* d_planes = nullptr;
-    act_t* d_trunk[2] = {nullptr, nullptr};
-    act_t* d_exp[2] = {nullptr, nullptr};
-    act_t* d_pol_shared = nullptr;
-    float* d_logits = nullptr;
-    act_t* d_vfeat = nullptr;
+    act_t* d_planes = nullptr;      // [B][74][64] network input (NCHW, the reference's obs layout)
+    act_t* d_trunk = nullptr;       // [B][384][64], updated in place by the trunk kernels
+    act_t* d_pol_shared = nullptr;  // [B][384][64]
+    float* d_logits = nullptr;      // [B][146][64] fp32 (fused path)
+    __half* d_pi = nullptr;         // [B][146][64] fp16 (reference-shaped path): A = ch 0..72, B = 73..145
+    act_t* d_vfeat = nullptr;       // [B][16][64]
     float* d_raw5 = nullptr;
-    float* d_gate = nullptr;
-    __half *d_value_h = nullptr, *d_wdl_h = nullptr, *d_ml_h = nullptr, *d_pi_a = nullptr,
-           *d_pi_b = nullptr;
+    float* d_sums = nullptr;        // [B][384] channel sums for the next ECA gate
+    float* d_gate = nullptr;        // [B][384]
+    __half *d_value_h = nullptr, *d_wdl_h = nullptr, *d_ml_h = nullptr;
     // pinned host mirrors (engine-owned outputs, engine.h:45-51)
     hm_packed_pos* h_pos = nullptr;
     uint32_t* h_moves = nullptr;
@@ -122,11 +120,11 @@ struct Worker {
     float* h_priors = nullptr;
     float* h_values = nullptr;
     float* h_raw5 = nullptr;
-    __half* h_obs = nullptr;
+    __half* h_obs = nullptr;        // staging of runInference's float -> half conversion
     __half *h_value = nullptr, *h_wdl = nullptr, *h_ml = nullptr, *h_pi_a = nullptr,
            *h_pi_b = nullptr;
 
-    std::vector<Op> ops_trunk;    // stem .. heads (planes NHWC in -> logits/raw5)
+    std::vector<Op> ops_trunk;    // stem .. policy trunk + value head (planes in -> features)
     std::vector<Op> ops_dense_in, ops_dense_out;   // reference-shaped pre/post
     std::vector<Op> ops_fused_in, ops_fused_out;   // packed-position pre/post
     cudaGraphExec_t graph_dense = nullptr, graph_fused = nullptr;

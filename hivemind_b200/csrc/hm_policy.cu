@@ -86,10 +86,10 @@ void launch_policy_indices(const uint32_t* moves, const uint8_t* stm_black, int 
 // one warp per (position, board).  exp() and the sum are evaluated in double so that the
 // float priors agree with the reference's (float exp, double sum) to the last ulp or one.
 // ---------------------------------------------------------------------------------------
-struct LogitsNHWC {
-    const float* base;  // [pos*64+sq][POLICY_LD], col = board*73 + ch
+struct LogitsPacked {
+    const float* base;  // [pos][2*73][64]: the reference's ch*64+sq index per board, boards A|B stacked
     __device__ __forceinline__ float at(int pos, int board, int idx) const {
-        return base[(static_cast<size_t>(pos) * 64 + (idx & 63)) * POLICY_LD + board * 73 + (idx >> 6)];
+        return base[(static_cast<size_t>(pos) * 2 + board) * HM_NB_POLICY_VALUES + idx];
     }
 };
 struct LogitsDenseHalf {
@@ -177,13 +177,13 @@ policy_priors_kernel(L logits, const hm_packed_pos* __restrict__ pos, int n_pos,
         priors[lo + i] = static_cast<float>(static_cast<double>(priors[lo + i]) / sum);
 }
 
-void launch_policy_priors_nhwc(const float* logits, const hm_packed_pos* pos, int n_pos,
+void launch_policy_priors_packed(const float* logits, const hm_packed_pos* pos, int n_pos,
                                const uint32_t* moves, const uint32_t* offsets, float* priors,
                                cudaStream_t s) {
     if (n_pos <= 0) return;
     const int warps = 2 * n_pos;
-    policy_priors_kernel<LogitsNHWC><<<(warps + 3) / 4, 128, 0, s>>>(LogitsNHWC{logits}, pos, n_pos,
-                                                                    moves, offsets, priors);
+    policy_priors_kernel<LogitsPacked><<<(warps + 3) / 4, 128, 0, s>>>(LogitsPacked{logits}, pos, n_pos,
+                                                                      moves, offsets, priors);
 }
 void launch_policy_priors_dense(const __half* pi_a, const __half* pi_b, const hm_packed_pos* pos,
                                 int n_pos, const uint32_t* moves, const uint32_t* offsets,

@@ -78,6 +78,26 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const void* tmap, ui
         : "memory");
 }
 
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const void* tmap, uint64_t* bar,
+                                            int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(smem_u32(smem_dst)),
+        "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+// shared -> global tile store (bulk async group)
+__device__ __forceinline__ void tma_store_3d(const void* tmap, const void* smem_src, int c0, int c1,
+                                             int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(tmap),
+        "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // 1-D bulk copy global -> shared (size multiple of 16, 16-byte aligned), completes on mbarrier
 __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes,
                                              uint64_t* bar) {
@@ -174,12 +194,29 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
     d |= static_cast<uint64_t>(2) << 61;
     return d;
 }
+// MN-major operand tile with the 128-byte swizzle (canonical layout, in 16-byte units,
+// ((8,n),(8,k)):((1,LBO),(8,SBO)) — cute/atom/mma_traits_sm100.hpp): a row of 64 MN-contiguous
+// 16-bit elements (128 B) per K index, 8 K rows per 1024-byte group; `lbo` = bytes between
+// 64-element MN atoms, `sbo` = bytes between 8-row K groups.
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+    d |= static_cast<uint64_t>((lbo >> 4) & 0x3FFFu) << 16;
+    d |= static_cast<uint64_t>((sbo >> 4) & 0x3FFFu) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(2) << 61;
+    return d;
+}
 // Instruction descriptor, kind::f16: D = fp32, A = B = 16-bit (fmt 0 = F16, 1 = BF16), both
 // K-major, dense.
 //   bits [4,6) c_format = 1 (F32); [7,10) a_format; [10,13) b_format
 //   bit 15 a_major = 0 (K); bit 16 b_major = 0 (K); [17,23) N >> 3; [24,29) M >> 4
 __host__ __device__ constexpr uint32_t umma_idesc_16(uint32_t M, uint32_t N, uint32_t fmt) {
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+// same with A K-major and B MN-major (bit 16 b_major = 1)
+__host__ __device__ constexpr uint32_t umma_idesc_16_bmn(uint32_t M, uint32_t N, uint32_t fmt) {
+    return umma_idesc_16(M, N, fmt) | (1u << 16);
 }
 
 }  // namespace hm

@@ -1,0 +1,368 @@
+// hm_trunk.cuh — a run of consecutive RISEv3 bottleneck blocks as ONE kernel (SURVEY.md §8a
+// rows F2a-F2d; reference builder_util.py:445-483):
+//
+//   per block:  y = relu(pw1(x) + b1);  z = relu(dw_kxk(y) + bd);  x <- x + pw2(z) + b2
+//
+// Everything is channel-major ("transposed"): output channels are the MMA M dimension (TMEM
+// lanes), the 128 board squares of the CTA's two positions are the N dimension (TMEM columns):
+//
+//   D1[128 op-channels x 128 sq]  = W1[chunk rows, 384] * X[384 x 128 sq]
+//   D2[384 channels    x 128 sq] += W2[:, chunk cols]   * Z[128 op-channels x 128 sq]
+//
+// so a compute thread that reads its TMEM lane owns ONE channel and all 64 squares of one
+// position: the depthwise k x k convolution, both ReLUs, the residual add and the ECA channel
+// sum are private register arithmetic — no shared-memory exchange, no shuffles.  The expanded
+// tensor (up to 1152 channels) never leaves the SM, and the trunk activation X stays resident
+// in shared memory across ALL blocks of the run (updated in place by the block epilogue): per
+// run it is read from HBM once and written once.
+//
+// Shared memory: X  [6][2 pos][64 ch][64 sq] 16-bit, MN-major 128-byte-swizzled = B operand of pw1
+//                Z  2 x [2][2 pos][64 ch][64 sq]                                 = B operand of pw2
+//                ring of 4 x 16 KB weight tiles [128 rows x 64 K] K-major        = A operands
+// TMEM (512 columns): D2 = 3 x 128 columns, D1 = 128 columns.
+// Warps (320 threads): 0 = TMA producer, 1 = MMA issuer, 2-9 = compute (lane quarter = warp & 3,
+// position = (warp - 2) >> 2).
+#pragma once
+#include <cuda.h>
+#include "hm_ptx.cuh"
+
+namespace hm {
+
+constexpr int TR_MAX_BLOCKS = 16;
+constexpr int TR_PAR_FLOATS = 27 * 128;  // per 128-channel chunk: b1 | dw bias | 25 taps, each [128]
+
+struct TrunkBlock {
+    int chunk0;    // first global chunk (row block of W1cat / W2cat, entry of par)
+    int n_chunks;  // ceil(cop / 128)
+    int ksize;     // 3 or 5
+    int bias2_off; // offset into bias2 (floats)
+};
+struct TrunkParams {
+    int n_blocks;
+    TrunkBlock blk[TR_MAX_BLOCKS];
+    const float* par;    // [chunk][TR_PAR_FLOATS]
+    const float* bias2;  // [...][384]
+    const float* gate;   // [pos][384] ECA gate of the run's first block, or nullptr
+    float* sums;         // [pos][384] channel sums (over 64 squares) of the run's output, or nullptr
+};
+
+constexpr int TR_THREADS = 320;
+constexpr int TR_COMPUTE = 256;
+constexpr int TR_SLOTS = 4;
+constexpr int TR_SLOT_BYTES = 16384;
+constexpr int TR_X_OFF = 0;
+constexpr int TR_Z_OFF = 6 * 16384;
+constexpr int TR_RING_OFF = TR_Z_OFF + 2 * 32768;
+constexpr int TR_BAR_OFF = TR_RING_OFF + TR_SLOTS * TR_SLOT_BYTES;
+constexpr int TR_SMEM = TR_BAR_OFF + 256;
+
+enum {
+    TB_X_FULL = 0, TB_X_READY, TB_D1_FULL, TB_D1_EMPTY, TB_D2_FULL,
+    TB_Z_FULL,                      // 2
+    TB_Z_EMPTY = TB_Z_FULL + 2,     // 2
+    TB_SLOT_FULL = TB_Z_EMPTY + 2,  // TR_SLOTS
+    TB_SLOT_EMPTY = TB_SLOT_FULL + TR_SLOTS,
+    TB_COUNT = TB_SLOT_EMPTY + TR_SLOTS
+};
+
+// k-th completion (k = 0, 1, ...) of a "full"-type barrier
+__device__ __forceinline__ void tr_wait_full(uint64_t* bar, uint32_t k) { mbar_wait(bar, k & 1); }
+// k-th reuse of a resource: free for k = 0, then needs the (k-1)-th completion of its "empty" barrier
+__device__ __forceinline__ void tr_wait_empty(uint64_t* bar, uint32_t k) { mbar_wait(bar, (k & 1) ^ 1); }
+
+// depthwise k x k on one channel of one board held in registers: out[s] = relu(bd + sum w*y)
+template <int KS>
+__device__ __forceinline__ void dw_board(const float (&y)[64], const float (&w)[KS * KS], float bd,
+                                         uint32_t (&packed)[32]) {
+    constexpr int H = KS / 2;
+#pragma unroll
+    for (int yo = 0; yo < 8; ++yo) {
+        float o[8];
+#pragma unroll
+        for (int xo = 0; xo < 8; ++xo) {
+            float acc = bd;
+#pragma unroll
+            for (int ky = 0; ky < KS; ++ky) {
+                const int yy = yo + ky - H;
+                if (yy < 0 || yy > 7) continue;
+#pragma unroll
+                for (int kx = 0; kx < KS; ++kx) {
+                    const int xx = xo + kx - H;
+                    if (xx < 0 || xx > 7) continue;
+                    acc = fmaf(y[yy * 8 + xx], w[ky * KS + kx], acc);
+                }
+            }
+            o[xo] = fmaxf(acc, 0.0f);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) packed[yo * 4 + j] = pack_act2(o[2 * j], o[2 * j + 1]);
+    }
+}
+
+template <int KS>
+__device__ __forceinline__ void trunk_chunk(const float* __restrict__ par, int r, uint32_t tm_d1,
+                                            uint64_t* bars, uint32_t d1_n, uint32_t z_n,
+                                            uint8_t* zrow, int lane) {
+    // parameters of this thread's channel (issued before the wait so they are in flight)
+    float w[KS * KS];
+#pragma unroll
+    for (int t = 0; t < KS * KS; ++t) w[t] = __ldg(par + 256 + t * 128 + r);
+    const float b1 = __ldg(par + r);
+    const float bd = __ldg(par + 128 + r);
+    float y[64];
+    tr_wait_full(&bars[TB_D1_FULL], d1_n);
+    tc_fence_after();
+    {
+        uint32_t a0[32], a1[32];
+        tmem_ld_32x32b_x32(tm_d1, a0);
+        tmem_ld_32x32b_x32(tm_d1 + 32, a1);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            y[j] = fmaxf(__uint_as_float(a0[j]) + b1, 0.0f);
+            y[32 + j] = fmaxf(__uint_as_float(a1[j]) + b1, 0.0f);
+        }
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bars[TB_D1_EMPTY]);  // D1 is free as soon as it is in registers
+    uint32_t packed[32];
+    dw_board<KS>(y, w, bd, packed);
+    const uint32_t zb = z_n & 1;
+    tr_wait_empty(&bars[TB_Z_EMPTY + zb], z_n >> 1);
+    const int key = r & 7;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<uint4*>(zrow + zb * 32768 + ((j ^ key) << 4)) =
+            make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bars[TB_Z_FULL + zb]);
+}
+
+__global__ void __launch_bounds__(TR_THREADS, 1)
+trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUtensorMap tmX,
+             const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2) {
+    extern __shared__ __align__(1024) uint8_t tr_smem[];
+    uint8_t* smem = tr_smem;
+    if (smem_u32(smem) & 1023u) __trap();  // swizzle atoms need 1024-byte alignment
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TR_BAR_OFF);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + TB_COUNT);
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int tile = blockIdx.x;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmX);
+        tma_prefetch_desc(&tmW1);
+        tma_prefetch_desc(&tmW2);
+        for (int i = 0; i < TB_COUNT; ++i) {
+            uint32_t count = 1;
+            if (i == TB_X_READY || i == TB_D1_EMPTY || i == TB_Z_FULL || i == TB_Z_FULL + 1) count = 8;
+            mbar_init(&bars[i], count);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tm_d2 = tmem_base;
+    const uint32_t tm_d1 = tmem_base + 384u;
+
+    if (warp == 0) {
+        // ================================ TMA producer ================================
+        if (lane == 0) {
+            mbar_arrive_expect_tx(&bars[TB_X_FULL], 6 * 16384);
+            for (int kb = 0; kb < 6; ++kb)
+                tma_load_3d(smem + TR_X_OFF + kb * 16384, &tmX, &bars[TB_X_FULL], 0, kb * 64, tile * 2);
+            uint32_t slot_n = 0;
+            auto stage = [&](const CUtensorMap* tm, int c0, int c1) {
+                const uint32_t sl = slot_n % TR_SLOTS;
+                tr_wait_empty(&bars[TB_SLOT_EMPTY + sl], slot_n / TR_SLOTS);
+                mbar_arrive_expect_tx(&bars[TB_SLOT_FULL + sl], TR_SLOT_BYTES);
+                tma_load_2d(smem + TR_RING_OFF + sl * TR_SLOT_BYTES, tm, &bars[TB_SLOT_FULL + sl], c0, c1);
+                ++slot_n;
+            };
+            for (int b = 0; b < p.n_blocks; ++b) {
+                const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks;
+                for (int kb = 0; kb < 6; ++kb) stage(&tmW1, kb * 64, g0 * 128);
+                for (int c = 0; c < nch; ++c) {
+                    if (c + 1 < nch)
+                        for (int kb = 0; kb < 6; ++kb) stage(&tmW1, kb * 64, (g0 + c + 1) * 128);
+                    for (int m = 0; m < 3; ++m)
+                        for (int kh = 0; kh < 2; ++kh) stage(&tmW2, kh * 64, (g0 + c) * 384 + m * 128);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer ================================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
+            uint32_t slot_n = 0, d1_n = 0, z_n = 0;
+            const uint32_t x_addr = smem_u32(smem + TR_X_OFF);
+            const uint32_t z_addr = smem_u32(smem + TR_Z_OFF);
+            const uint32_t ring = smem_u32(smem + TR_RING_OFF);
+            auto pw1 = [&]() {
+                tr_wait_empty(&bars[TB_D1_EMPTY], d1_n);
+                tc_fence_after();
+                for (int kb = 0; kb < 6; ++kb) {
+                    const uint32_t sl = slot_n % TR_SLOTS;
+                    tr_wait_full(&bars[TB_SLOT_FULL + sl], slot_n / TR_SLOTS);
+                    tc_fence_after();
+                    const uint64_t a_desc = umma_desc_sw128(ring + sl * TR_SLOT_BYTES);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint64_t b_desc = umma_desc_mn_sw128(x_addr + kb * 16384 + k * 2048, 8192, 1024);
+                        umma_f16(tm_d1, a_desc + 2 * k, b_desc, idesc, (kb | k) ? 1u : 0u);
+                    }
+                    umma_commit(&bars[TB_SLOT_EMPTY + sl]);
+                    ++slot_n;
+                }
+                umma_commit(&bars[TB_D1_FULL]);
+                ++d1_n;
+            };
+            for (int b = 0; b < p.n_blocks; ++b) {
+                const int nch = p.blk[b].n_chunks;
+                tr_wait_full(&bars[TB_X_READY], b);  // X (scaled / updated in place) is ready; D2 drained
+                tc_fence_after();
+                pw1();
+                for (int c = 0; c < nch; ++c) {
+                    if (c + 1 < nch) pw1();
+                    const uint32_t zb = z_n & 1;
+                    tr_wait_full(&bars[TB_Z_FULL + zb], z_n >> 1);
+                    tc_fence_after();
+                    for (int m = 0; m < 3; ++m) {
+                        for (int kh = 0; kh < 2; ++kh) {
+                            const uint32_t sl = slot_n % TR_SLOTS;
+                            tr_wait_full(&bars[TB_SLOT_FULL + sl], slot_n / TR_SLOTS);
+                            tc_fence_after();
+                            const uint64_t a_desc = umma_desc_sw128(ring + sl * TR_SLOT_BYTES);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const uint64_t b_desc = umma_desc_mn_sw128(
+                                    z_addr + zb * 32768 + kh * 16384 + k * 2048, 8192, 1024);
+                                umma_f16(tm_d2 + m * 128, a_desc + 2 * k, b_desc, idesc, (c | kh | k) ? 1u : 0u);
+                            }
+                            umma_commit(&bars[TB_SLOT_EMPTY + sl]);
+                            ++slot_n;
+                        }
+                    }
+                    umma_commit(&bars[TB_Z_EMPTY + zb]);
+                    ++z_n;
+                }
+                umma_commit(&bars[TB_D2_FULL]);
+            }
+        }
+    } else {
+        // ================================ compute warps ================================
+        const int q = warp & 3;             // TMEM lane quarter this warp may access
+        const int h = (warp - 2) >> 2;      // position of the tile handled by this warp
+        const int r = q * 32 + lane;        // channel within a 128-channel chunk / M block
+        const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+        const int pos = tile * 2 + h;
+        const int key = r & 7;
+        // this thread's 128-byte row inside a [2 pos][64 ch][64 sq] block
+        const uint32_t row_off = (r >> 6) * 16384 + h * 8192 + (r & 63) * 128;
+
+        // ---- segment input: optional ECA gate (builder_util.py:77-80, 481-483), x' = x * gate ----
+        tr_wait_full(&bars[TB_X_FULL], 0);
+        if (p.gate != nullptr) {
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+                const float g = __ldg(p.gate + static_cast<size_t>(pos) * 384 + m * 128 + r);
+                uint8_t* xrow = smem + TR_X_OFF + m * 32768 + row_off;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    uint4* px = reinterpret_cast<uint4*>(xrow + ((j ^ key) << 4));
+                    uint4 v = *px;
+                    float2 a = unpack_act2(v.x), b = unpack_act2(v.y), c = unpack_act2(v.z), d = unpack_act2(v.w);
+                    v.x = pack_act2(a.x * g, a.y * g);
+                    v.y = pack_act2(b.x * g, b.y * g);
+                    v.z = pack_act2(c.x * g, c.y * g);
+                    v.w = pack_act2(d.x * g, d.y * g);
+                    *px = v;
+                }
+            }
+            fence_proxy_async_smem();
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars[TB_X_READY]);
+
+        uint32_t d1_n = 0, z_n = 0;
+        for (int b = 0; b < p.n_blocks; ++b) {
+            const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks, ks = p.blk[b].ksize;
+            for (int c = 0; c < nch; ++c) {
+                const float* par = p.par + static_cast<size_t>(g0 + c) * TR_PAR_FLOATS;
+                uint8_t* zrow = smem + TR_Z_OFF + row_off;
+                if (ks == 3)
+                    trunk_chunk<3>(par, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane);
+                else
+                    trunk_chunk<5>(par, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane);
+                ++d1_n;
+                ++z_n;
+            }
+            // ---- block epilogue: x <- x + D2 + b2, in place in shared memory ----
+            const bool last = (b + 1 == p.n_blocks);
+            const float* b2 = p.bias2 + p.blk[b].bias2_off;
+            float bias[3];
+#pragma unroll
+            for (int m = 0; m < 3; ++m) bias[m] = __ldg(b2 + m * 128 + r);
+            tr_wait_full(&bars[TB_D2_FULL], b);
+            tc_fence_after();
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+                uint32_t a0[32], a1[32];
+                tmem_ld_32x32b_x32(tm_d2 + lane_off + m * 128 + h * 64, a0);
+                tmem_ld_32x32b_x32(tm_d2 + lane_off + m * 128 + h * 64 + 32, a1);
+                uint8_t* xrow = smem + TR_X_OFF + m * 32768 + row_off;
+                tmem_ld_wait();
+                float s = 0.0f;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    uint4* px = reinterpret_cast<uint4*>(xrow + ((j ^ key) << 4));
+                    const uint4 v = *px;
+                    const uint32_t ru[4] = {v.x, v.y, v.z, v.w};
+                    uint32_t ou[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int i = j * 8 + e * 2;
+                        const float2 res = unpack_act2(ru[e]);
+                        const float v0 = __uint_as_float(i < 32 ? a0[i] : a1[i - 32]) + bias[m] + res.x;
+                        const float v1 = __uint_as_float(i < 32 ? a0[i + 1] : a1[i - 31]) + bias[m] + res.y;
+                        ou[e] = pack_act2(v0, v1);
+                        const float2 rd = unpack_act2(ou[e]);
+                        s += rd.x + rd.y;
+                    }
+                    *px = make_uint4(ou[0], ou[1], ou[2], ou[3]);
+                }
+                if (last && p.sums != nullptr) p.sums[static_cast<size_t>(pos) * 384 + m * 128 + r] = s;
+            }
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (!last) {
+                if (lane == 0) mbar_arrive(&bars[TB_X_READY]);
+            }
+        }
+        // ---- run output: shared-memory tile -> global (TMA store) ----
+        named_bar_sync(1, TR_COMPUTE);
+        if (threadIdx.x == 64) {
+            for (int kb = 0; kb < 6; ++kb) tma_store_3d(&tmX, smem + TR_X_OFF + kb * 16384, 0, kb * 64, tile * 2);
+            bulk_commit_group();
+            bulk_wait_group0();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace hm

@@ -1,8 +1,9 @@
 """Stage-by-stage GPU bring-up check (verbose; the pass/fail version lives in tests/).
 
 Compares every inspectable activation of the CUDA path with the fp32 oracle, first on a
-truncated 1-block network (so stem / pw1 / dw / pw2 / heads are each visible), then on the
-full network.  Usage:  python tools/diagnose.py [n_blocks ...]
+truncated network, then on the full network.  HM_TRUNK_STOP=k in the environment stops the trunk
+after block k-1 (0 = stem only) so the intermediate activation is inspectable.
+Usage:  python tools/diagnose.py [n_blocks ...]
 """
 import os
 import sys
@@ -30,10 +31,6 @@ def stats(name, got, want):
     return d.max()
 
 
-def nhwc_to_nchw(a, n, c):
-    return a.reshape(n, 64, c).transpose(0, 2, 1).reshape(n, c, 8, 8)
-
-
 def run(n_blocks, folded_full, packed, moves, offsets, oracle):
     keep = {k: v for k, v in folded_full.items() if not k.startswith("b") or int(k[1:k.index(".")]) < n_blocks}
     blob = W.write_hvmw(None, keep)
@@ -44,22 +41,23 @@ def run(n_blocks, folded_full, packed, moves, offsets, oracle):
     t = time.time()
     assert eng.loadNetworkFromMemory(blob), "load failed"
     print(f"[{n_blocks} blocks] load+graph capture {time.time() - t:.2f}s", flush=True)
+    if os.environ.get("HM_CHECKED"):
+        # stage the inputs without running the graph is not possible; run launch by launch
+        print("  checked pass:", eng.profilePass(), flush=True)
     res = eng.evaluatePositions(packed, moves, offsets)
     assert res is not None, "evaluate failed"
     priors, values, raw = res
-    pl = eng.debugFetch("planes").reshape(n, 64, 80)[:, :, :74].transpose(0, 2, 1).reshape(n, 74, 8, 8)
-    stats("planes(nhwc)", pl, planes)
-    if n_blocks == 1:
-        stats("stem", nhwc_to_nchw(eng.debugFetch("stem"), n, 384), ref["inter"]["stem"])
-    last = n_blocks - 1
-    stats(f"block{last}", nhwc_to_nchw(eng.debugFetch(f"block{last}"), n, 384), ref["inter"][f"block{last}"])
-    stats("value_feat", nhwc_to_nchw(eng.debugFetch("value_feat"), n, 16), ref["inter"]["value_feat"])
-    stats("policy_shared", nhwc_to_nchw(eng.debugFetch("policy_shared"), n, 384), ref["inter"]["policy_shared"])
-    lg = eng.debugFetch("logits").reshape(n, 64, 160)
-    pa = lg[:, :, :73].transpose(0, 2, 1).reshape(n, 4672)
-    pb = lg[:, :, 73:146].transpose(0, 2, 1).reshape(n, 4672)
-    stats("pi_a", pa, ref["pi_a"])
-    stats("pi_b", pb, ref["pi_b"])
+    stats("planes", eng.debugFetch("planes").reshape(n, 74, 8, 8), planes)
+    stop = os.environ.get("HM_TRUNK_STOP")
+    last = n_blocks - 1 if stop is None else min(n_blocks, int(stop)) - 1
+    want_trunk = ref["inter"]["stem"] if last < 0 else ref["inter"][f"block{last}"]
+    stats("stem" if last < 0 else f"block{last}", eng.debugFetch("trunk").reshape(n, 384, 8, 8), want_trunk)
+    if stop is None:
+        stats("value_feat", eng.debugFetch("value_feat").reshape(n, 16, 8, 8), ref["inter"]["value_feat"])
+        stats("policy_shared", eng.debugFetch("policy_shared").reshape(n, 384, 8, 8), ref["inter"]["policy_shared"])
+    lg = eng.debugFetch("logits").reshape(n, 2, 4672)
+    stats("pi_a", lg[:, 0], ref["pi_a"])
+    stats("pi_b", lg[:, 1], ref["pi_b"])
     stats("value", raw[:, 0], ref["value"])
     stats("wdl", raw[:, 1:4], ref["wdl"])
     stats("moves_left", raw[:, 4], ref["moves_left"])
