@@ -397,6 +397,42 @@ int hm_engine_bench_resident(hm_engine* h, size_t worker, int iters, float* ms_t
     HM_CATCH(0)
 }
 
+int hm_engine_bench_resident_multi(hm_engine* h, int n_workers, int iters, float* ms_total,
+                                   int* launches_per_pass) {
+    HM_TRY
+    if (!h || n_workers < 1 || n_workers > h->e.n_workers) { set_error("bad worker count"); return 0; }
+    if (!use_device(h)) return 0;
+    for (int i = 0; i < n_workers; ++i)
+        if (h->e.workers[i]->pending) { set_error("worker busy"); return 0; }
+    Worker* w0 = h->e.workers[0].get();
+    cudaEvent_t e0, e1;
+    std::vector<cudaEvent_t> joins(n_workers, nullptr);
+    if (!cuda_ok(cudaEventCreate(&e0), "event") || !cuda_ok(cudaEventCreate(&e1), "event")) return 0;
+    bool ok = cuda_ok(cudaEventRecord(e0, w0->stream), "record");
+    for (int i = 1; ok && i < n_workers; ++i) {
+        ok = cuda_ok(cudaEventCreateWithFlags(&joins[i], cudaEventDisableTiming), "event") &&
+             cuda_ok(cudaStreamWaitEvent(h->e.workers[i]->stream, e0, 0), "fork");
+    }
+    for (int it = 0; ok && it < iters; ++it) {
+        Worker* w = h->e.workers[it % n_workers].get();
+        ok = cuda_ok(cudaGraphLaunch(w->graph_fused, w->stream), "graph launch");
+    }
+    for (int i = 1; ok && i < n_workers; ++i)
+        ok = cuda_ok(cudaEventRecord(joins[i], h->e.workers[i]->stream), "record") &&
+             cuda_ok(cudaStreamWaitEvent(w0->stream, joins[i], 0), "join");
+    ok = ok && cuda_ok(cudaEventRecord(e1, w0->stream), "record") && cuda_ok(cudaEventSynchronize(e1), "event sync");
+    float ms = 0.f;
+    if (ok) ok = cuda_ok(cudaEventElapsedTime(&ms, e0, e1), "elapsed");
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    for (auto ev : joins) if (ev) cudaEventDestroy(ev);
+    if (ms_total) *ms_total = ms;
+    if (launches_per_pass)
+        *launches_per_pass = static_cast<int>(w0->ops_fused_in.size() + w0->ops_trunk.size() + w0->ops_fused_out.size());
+    return ok ? 1 : 0;
+    HM_CATCH(0)
+}
+
 int hm_engine_profile_pass(hm_engine* h, size_t worker, hm_kernel_time* out, int cap, int* n) {
     HM_TRY
     Worker* w = get_worker(h, worker);

@@ -29,11 +29,10 @@ __host__ __device__ __forceinline__ act_t float_to_act(float v) { return __float
 using act_t = __half;
 constexpr uint32_t UMMA_FMT_16 = 0;  // F16
 __device__ __forceinline__ uint32_t pack_act2(float lo, float hi) {
-    // saturate instead of overflowing to inf
-    lo = fminf(fmaxf(lo, -65504.0f), 65504.0f);
-    hi = fminf(fmaxf(hi, -65504.0f), 65504.0f);
-    __half2 v = __floats2half2_rn(lo, hi);
-    return *reinterpret_cast<uint32_t*>(&v);
+    // one F2FP.SATFINITE: round to nearest, saturate to +-65504 instead of overflowing to inf
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
 }
 __device__ __forceinline__ float2 unpack_act2(uint32_t u) {
     __half2 v = *reinterpret_cast<__half2*>(&u);

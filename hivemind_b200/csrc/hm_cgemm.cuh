@@ -33,7 +33,7 @@ struct CgemmParams {
     int m_blocks;       // ceil(cout / 128)
     int n_valid;        // cout: channels actually stored
     int ksize;          // 1 or 3
-    int kblocks;        // Cpad / 64 per tap
+    int kblocks;        // Cpad / 64 per tap (even)
     const float* bias;  // [cout] or nullptr
     void* out;          // [pos][out_channels][64], act_t or fp32
     int out_channels;   // channel count of the output tensor
@@ -43,7 +43,10 @@ struct CgemmParams {
 
 constexpr int CG_THREADS = 192;
 constexpr int CG_STAGES = 3;
-constexpr int CG_STAGE_BYTES = 32768;  // A 16 KB + B 16 KB
+// One stage = 128 K values: two A tiles (2 x 16 KB) + two B blocks (2 x 16 KB) behind ONE barrier
+// pair, i.e. 8 MMAs (512 tensor-pipe cycles) per barrier round trip of the single-thread producer
+// and issuer loops (a 4-MMA stage cannot hide it: tools/probes/probe_mmaring.cu).
+constexpr int CG_STAGE_BYTES = 65536;
 constexpr int CG_SMEM = CG_STAGES * CG_STAGE_BYTES + 256 + 1024;
 
 __global__ void __launch_bounds__(CG_THREADS)
@@ -61,8 +64,6 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x / p.m_blocks;
     const int mb = blockIdx.x - tile * p.m_blocks;
-    const int taps = p.ksize * p.ksize;
-    const int k_iters = taps * p.kblocks;
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmW);
@@ -84,44 +85,54 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    const int kpairs = p.kblocks >> 1;
     if (warp == 0) {
         if (lane == 0) {
-            const int half = p.ksize >> 1;
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int it = 0; it < k_iters; ++it) {
-                const int tap = it / p.kblocks;
-                const int kb = it - tap * p.kblocks;
-                const int dy = tap / p.ksize - half;
-                mbar_wait(&empty_bar[stage], phase ^ 1);
-                uint8_t* a_dst = smem + stage * CG_STAGE_BYTES;
-                mbar_arrive_expect_tx(&full_bar[stage], CG_STAGE_BYTES);
-                tma_load_2d(a_dst, &tmW, &full_bar[stage], it * 64, mb * 128);
-                tma_load_3d(a_dst + 16384, &tmX, &full_bar[stage], 8 * dy, kb * 64, tile * 2);
-                if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
+            int stage = 0, kcol = 0;
+            uint32_t phase = 1;
+            const int row0 = mb * 128, pos0 = tile * 2;
+            for (int ky = 0; ky < p.ksize; ++ky) {
+                const int sq0 = 8 * (ky - (p.ksize >> 1));   // vertical tap offset as a square shift
+                for (int kx = 0; kx < p.ksize; ++kx) {
+                    for (int kp = 0; kp < kpairs; ++kp, kcol += 128) {
+                        mbar_wait(&empty_bar[stage], phase);
+                        uint8_t* dst = smem + stage * CG_STAGE_BYTES;
+                        mbar_arrive_expect_tx(&full_bar[stage], CG_STAGE_BYTES);
+                        tma_load_2d(dst, &tmW, &full_bar[stage], kcol, row0);
+                        tma_load_2d(dst + 16384, &tmW, &full_bar[stage], kcol + 64, row0);
+                        tma_load_3d(dst + 32768, &tmX, &full_bar[stage], sq0, kp * 128, pos0);
+                        tma_load_3d(dst + 49152, &tmX, &full_bar[stage], sq0, kp * 128 + 64, pos0);
+                        if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
+                    }
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
+            const uint64_t a0 = umma_desc_sw128(smem_u32(smem));
+            const uint64_t b0 = umma_desc_mn_sw128(smem_u32(smem) + 32768, 8192, 1024);
             int stage = 0;
             uint32_t phase = 0;
-            for (int it = 0; it < k_iters; ++it) {
-                const int tap = it / p.kblocks;
-                const int acc_i = tap % p.ksize;              // horizontal offset dx + 1 (0 for 1x1)
-                const bool first = tap < p.ksize && it == tap * p.kblocks;  // first tile of this accumulator
-                mbar_wait(&full_bar[stage], phase);
-                tc_fence_after();
-                const uint32_t a_addr = smem_u32(smem + stage * CG_STAGE_BYTES);
-                const uint64_t a_desc = umma_desc_sw128(a_addr);
+            for (int ky = 0; ky < p.ksize; ++ky) {
+                for (int kx = 0; kx < p.ksize; ++kx) {       // accumulator = horizontal offset kx
+                    const uint32_t d = tmem_base + kx * 128;
+                    for (int kp = 0; kp < kpairs; ++kp) {
+                        mbar_wait(&full_bar[stage], phase);
+                        tc_fence_after();
+                        const uint32_t so = stage * (CG_STAGE_BYTES / 16);
+                        const uint32_t acc0 = (ky | kp) ? 1u : 0u;  // first tile of this accumulator
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    // A: +32 B along K inside the swizzle row; B: +16 channel rows = 2 K groups
-                    const uint64_t b_desc = umma_desc_mn_sw128(a_addr + 16384 + k * 2048, 8192, 1024);
-                    umma_f16(tmem_base + acc_i * 128, a_desc + 2 * k, b_desc, idesc, (first && k == 0) ? 0u : 1u);
+                        for (int j = 0; j < 2; ++j) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                umma_f16(d, a0 + (so + j * 1024 + 2 * k), b0 + (so + j * 1024 + k * 128), idesc,
+                                         (j | k) ? 1u : acc0);
+                        }
+                        umma_commit(&empty_bar[stage]);
+                        if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
+                    }
                 }
-                umma_commit(&empty_bar[stage]);
-                if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
             }
             umma_commit(accum_bar);
         }

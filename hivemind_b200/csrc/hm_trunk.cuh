@@ -17,8 +17,8 @@
 // run it is read from HBM once and written once.
 //
 // Shared memory: X  [6][2 pos][64 ch][64 sq] 16-bit, MN-major 128-byte-swizzled = B operand of pw1
-//                Z  2 x [2][2 pos][64 ch][64 sq]                                 = B operand of pw2
-//                ring of 4 x 16 KB weight tiles [128 rows x 64 K] K-major        = A operands
+//                Z  [2][2 pos][64 ch][64 sq]                                     = B operand of pw2
+//                ring of 6 x 16 KB weight tiles [128 rows x 64 K] K-major        = A operands
 // TMEM (512 columns): D2 = 3 x 128 columns, D1 = 128 columns.
 // Warps (320 threads): 0 = TMA producer, 1 = MMA issuer, 2-9 = compute (lane quarter = warp & 3,
 // position = (warp - 2) >> 2).
@@ -48,21 +48,30 @@ struct TrunkParams {
 
 constexpr int TR_THREADS = 320;
 constexpr int TR_COMPUTE = 256;
-constexpr int TR_SLOTS = 4;
+// Weight ring: 6 slots of 16 KB = exactly one "group" (the 6 W1 tiles of a chunk's pw1, or the 6
+// W2 tiles of its pw2), so slot indices are compile-time inside the fully unrolled group loops and
+// the barrier parity simply toggles per group.  One full/empty barrier pair guards TWO slots
+// (32 KB, 8 MMAs): the single-thread producer / issuer loops pay ~100 cycles per barrier round
+// trip, which a 4-MMA (256-cycle) stage cannot hide (tools/probes/probe_mmaring.cu).
+constexpr int TR_SLOTS = 6;
+constexpr int TR_PAIRS = 3;
 constexpr int TR_SLOT_BYTES = 16384;
 constexpr int TR_X_OFF = 0;
 constexpr int TR_Z_OFF = 6 * 16384;
-constexpr int TR_RING_OFF = TR_Z_OFF + 2 * 32768;
+constexpr int TR_RING_OFF = TR_Z_OFF + 32768;
 constexpr int TR_BAR_OFF = TR_RING_OFF + TR_SLOTS * TR_SLOT_BYTES;
 constexpr int TR_SMEM = TR_BAR_OFF + 256;
 
+// X_READY[m] / D2_FULL[m] are per 128-channel output block m: the block epilogue of block m
+// (channels m*128..) overlaps the pw2 MMAs of blocks m+1.. and the next bottleneck block's first
+// pw1 starts on X blocks 2m, 2m+1 as soon as epilogue part m has rewritten them.
 enum {
-    TB_X_FULL = 0, TB_X_READY, TB_D1_FULL, TB_D1_EMPTY, TB_D2_FULL,
-    TB_Z_FULL,                      // 2
-    TB_Z_EMPTY = TB_Z_FULL + 2,     // 2
-    TB_SLOT_FULL = TB_Z_EMPTY + 2,  // TR_SLOTS
-    TB_SLOT_EMPTY = TB_SLOT_FULL + TR_SLOTS,
-    TB_COUNT = TB_SLOT_EMPTY + TR_SLOTS
+    TB_X_FULL = 0, TB_D1_FULL, TB_D1_EMPTY, TB_Z_FULL, TB_Z_EMPTY,
+    TB_X_READY,                               // 3
+    TB_D2_FULL = TB_X_READY + 3,              // 3
+    TB_PAIR_FULL = TB_D2_FULL + 3,            // TR_PAIRS
+    TB_PAIR_EMPTY = TB_PAIR_FULL + TR_PAIRS,  // TR_PAIRS
+    TB_COUNT = TB_PAIR_EMPTY + TR_PAIRS
 };
 
 // k-th completion (k = 0, 1, ...) of a "full"-type barrier
@@ -128,16 +137,15 @@ __device__ __forceinline__ void trunk_chunk(const float* __restrict__ par, int r
     if (lane == 0) mbar_arrive(&bars[TB_D1_EMPTY]);  // D1 is free as soon as it is in registers
     uint32_t packed[32];
     dw_board<KS>(y, w, bd, packed);
-    const uint32_t zb = z_n & 1;
-    tr_wait_empty(&bars[TB_Z_EMPTY + zb], z_n >> 1);
+    tr_wait_empty(&bars[TB_Z_EMPTY], z_n);  // pw2 of the previous chunk has consumed Z
     const int key = r & 7;
 #pragma unroll
     for (int j = 0; j < 8; ++j)
-        *reinterpret_cast<uint4*>(zrow + zb * 32768 + ((j ^ key) << 4)) =
+        *reinterpret_cast<uint4*>(zrow + ((j ^ key) << 4)) =
             make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
     fence_proxy_async_smem();
     __syncwarp();
-    if (lane == 0) mbar_arrive(&bars[TB_Z_FULL + zb]);
+    if (lane == 0) mbar_arrive(&bars[TB_Z_FULL]);
 }
 
 __global__ void __launch_bounds__(TR_THREADS, 1)
@@ -158,7 +166,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         tma_prefetch_desc(&tmW2);
         for (int i = 0; i < TB_COUNT; ++i) {
             uint32_t count = 1;
-            if (i == TB_X_READY || i == TB_D1_EMPTY || i == TB_Z_FULL || i == TB_Z_FULL + 1) count = 8;
+            if ((i >= TB_X_READY && i < TB_X_READY + 3) || i == TB_D1_EMPTY || i == TB_Z_FULL) count = 8;
             mbar_init(&bars[i], count);
         }
         fence_barrier_init();
@@ -180,22 +188,38 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             mbar_arrive_expect_tx(&bars[TB_X_FULL], 6 * 16384);
             for (int kb = 0; kb < 6; ++kb)
                 tma_load_3d(smem + TR_X_OFF + kb * 16384, &tmX, &bars[TB_X_FULL], 0, kb * 64, tile * 2);
-            uint32_t slot_n = 0;
-            auto stage = [&](const CUtensorMap* tm, int c0, int c1) {
-                const uint32_t sl = slot_n % TR_SLOTS;
-                tr_wait_empty(&bars[TB_SLOT_EMPTY + sl], slot_n / TR_SLOTS);
-                mbar_arrive_expect_tx(&bars[TB_SLOT_FULL + sl], TR_SLOT_BYTES);
-                tma_load_2d(smem + TR_RING_OFF + sl * TR_SLOT_BYTES, tm, &bars[TB_SLOT_FULL + sl], c0, c1);
-                ++slot_n;
+            // one group = 6 tiles = one lap over the ring; `par` is the empty-barrier parity of the lap
+            uint32_t par = 1;
+            auto group_w1 = [&](int g) {   // W1 rows [g*128, +128) x K blocks 0..5
+#pragma unroll
+                for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
+                    mbar_wait(&bars[TB_PAIR_EMPTY + b2], par);
+                    mbar_arrive_expect_tx(&bars[TB_PAIR_FULL + b2], 2 * TR_SLOT_BYTES);
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)
+                        tma_load_2d(smem + TR_RING_OFF + (2 * b2 + j) * TR_SLOT_BYTES, &tmW1,
+                                    &bars[TB_PAIR_FULL + b2], (2 * b2 + j) * 64, g * 128);
+                }
+                par ^= 1;
+            };
+            auto group_w2 = [&](int g) {   // W2 of chunk g: tile s = m*2 + kh -> rows g*384 + m*128, K half kh
+#pragma unroll
+                for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
+                    mbar_wait(&bars[TB_PAIR_EMPTY + b2], par);
+                    mbar_arrive_expect_tx(&bars[TB_PAIR_FULL + b2], 2 * TR_SLOT_BYTES);
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)   // pair b2 = output block m = b2, K halves kh = j
+                        tma_load_2d(smem + TR_RING_OFF + (2 * b2 + j) * TR_SLOT_BYTES, &tmW2,
+                                    &bars[TB_PAIR_FULL + b2], j * 64, g * 384 + b2 * 128);
+                }
+                par ^= 1;
             };
             for (int b = 0; b < p.n_blocks; ++b) {
                 const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks;
-                for (int kb = 0; kb < 6; ++kb) stage(&tmW1, kb * 64, g0 * 128);
+                group_w1(g0);
                 for (int c = 0; c < nch; ++c) {
-                    if (c + 1 < nch)
-                        for (int kb = 0; kb < 6; ++kb) stage(&tmW1, kb * 64, (g0 + c + 1) * 128);
-                    for (int m = 0; m < 3; ++m)
-                        for (int kh = 0; kh < 2; ++kh) stage(&tmW2, kh * 64, (g0 + c) * 384 + m * 128);
+                    if (c + 1 < nch) group_w1(g0 + c + 1);
+                    group_w2(g0 + c);
                 }
             }
         }
@@ -203,59 +227,59 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         // ================================ MMA issuer ================================
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
-            uint32_t slot_n = 0, d1_n = 0, z_n = 0;
-            const uint32_t x_addr = smem_u32(smem + TR_X_OFF);
-            const uint32_t z_addr = smem_u32(smem + TR_Z_OFF);
-            const uint32_t ring = smem_u32(smem + TR_RING_OFF);
-            auto pw1 = [&]() {
+            uint32_t d1_n = 0, z_n = 0, par = 0;
+            // descriptors differ only in the start-address field (16-byte units): hoist the bases
+            const uint64_t a0 = umma_desc_sw128(smem_u32(smem + TR_RING_OFF));
+            const uint64_t xd0 = umma_desc_mn_sw128(smem_u32(smem + TR_X_OFF), 8192, 1024);
+            const uint64_t zd0 = umma_desc_mn_sw128(smem_u32(smem + TR_Z_OFF), 8192, 1024);
+            auto pw1 = [&](int xblock) {   // xblock >= 0: first pw1 of bottleneck block `xblock`
                 tr_wait_empty(&bars[TB_D1_EMPTY], d1_n);
                 tc_fence_after();
-                for (int kb = 0; kb < 6; ++kb) {
-                    const uint32_t sl = slot_n % TR_SLOTS;
-                    tr_wait_full(&bars[TB_SLOT_FULL + sl], slot_n / TR_SLOTS);
-                    tc_fence_after();
-                    const uint64_t a_desc = umma_desc_sw128(ring + sl * TR_SLOT_BYTES);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint64_t b_desc = umma_desc_mn_sw128(x_addr + kb * 16384 + k * 2048, 8192, 1024);
-                        umma_f16(tm_d1, a_desc + 2 * k, b_desc, idesc, (kb | k) ? 1u : 0u);
+                for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
+                    if (xblock >= 0) tr_wait_full(&bars[TB_X_READY + b2], xblock);  // X blocks 2*b2, 2*b2+1 ready
+                    mbar_wait(&bars[TB_PAIR_FULL + b2], par);
+                    tc_fence_after();
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        const int kb = 2 * b2 + j;  // ring slot = K block of X
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_f16(tm_d1, a0 + (kb * 1024 + 2 * k), xd0 + (kb * 1024 + k * 128), idesc,
+                                     (kb | k) ? 1u : 0u);
                     }
-                    umma_commit(&bars[TB_SLOT_EMPTY + sl]);
-                    ++slot_n;
+                    umma_commit(&bars[TB_PAIR_EMPTY + b2]);
                 }
+                par ^= 1;
                 umma_commit(&bars[TB_D1_FULL]);
                 ++d1_n;
             };
             for (int b = 0; b < p.n_blocks; ++b) {
                 const int nch = p.blk[b].n_chunks;
-                tr_wait_full(&bars[TB_X_READY], b);  // X (scaled / updated in place) is ready; D2 drained
-                tc_fence_after();
-                pw1();
+                pw1(b);
                 for (int c = 0; c < nch; ++c) {
-                    if (c + 1 < nch) pw1();
-                    const uint32_t zb = z_n & 1;
-                    tr_wait_full(&bars[TB_Z_FULL + zb], z_n >> 1);
+                    if (c + 1 < nch) pw1(-1);
+                    tr_wait_full(&bars[TB_Z_FULL], z_n);
                     tc_fence_after();
-                    for (int m = 0; m < 3; ++m) {
-                        for (int kh = 0; kh < 2; ++kh) {
-                            const uint32_t sl = slot_n % TR_SLOTS;
-                            tr_wait_full(&bars[TB_SLOT_FULL + sl], slot_n / TR_SLOTS);
-                            tc_fence_after();
-                            const uint64_t a_desc = umma_desc_sw128(ring + sl * TR_SLOT_BYTES);
+                    const uint32_t acc0 = c > 0 ? 1u : 0u;
 #pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                const uint64_t b_desc = umma_desc_mn_sw128(
-                                    z_addr + zb * 32768 + kh * 16384 + k * 2048, 8192, 1024);
-                                umma_f16(tm_d2 + m * 128, a_desc + 2 * k, b_desc, idesc, (c | kh | k) ? 1u : 0u);
-                            }
-                            umma_commit(&bars[TB_SLOT_EMPTY + sl]);
-                            ++slot_n;
+                    for (int m = 0; m < TR_PAIRS; ++m) {   // pair = output channel block m
+                        mbar_wait(&bars[TB_PAIR_FULL + m], par);
+                        tc_fence_after();
+#pragma unroll
+                        for (int kh = 0; kh < 2; ++kh) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                umma_f16(tm_d2 + m * 128, a0 + ((2 * m + kh) * 1024 + 2 * k),
+                                         zd0 + (kh * 1024 + k * 128), idesc, (kh | k) ? 1u : acc0);
                         }
+                        umma_commit(&bars[TB_PAIR_EMPTY + m]);
+                        if (c + 1 == nch) umma_commit(&bars[TB_D2_FULL + m]);  // output block m complete
                     }
-                    umma_commit(&bars[TB_Z_EMPTY + zb]);
+                    par ^= 1;
+                    umma_commit(&bars[TB_Z_EMPTY]);
                     ++z_n;
                 }
-                umma_commit(&bars[TB_D2_FULL]);
             }
         }
     } else {
@@ -291,7 +315,11 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             fence_proxy_async_smem();
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bars[TB_X_READY]);
+        if (lane == 0) {
+            mbar_arrive(&bars[TB_X_READY + 0]);
+            mbar_arrive(&bars[TB_X_READY + 1]);
+            mbar_arrive(&bars[TB_X_READY + 2]);
+        }
 
         uint32_t d1_n = 0, z_n = 0;
         for (int b = 0; b < p.n_blocks; ++b) {
@@ -309,13 +337,12 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             // ---- block epilogue: x <- x + D2 + b2, in place in shared memory ----
             const bool last = (b + 1 == p.n_blocks);
             const float* b2 = p.bias2 + p.blk[b].bias2_off;
-            float bias[3];
-#pragma unroll
-            for (int m = 0; m < 3; ++m) bias[m] = __ldg(b2 + m * 128 + r);
-            tr_wait_full(&bars[TB_D2_FULL], b);
-            tc_fence_after();
-#pragma unroll
+            const bool want_sums = last && p.sums != nullptr;
+#pragma unroll 1
             for (int m = 0; m < 3; ++m) {
+                const float bias = __ldg(b2 + m * 128 + r);
+                tr_wait_full(&bars[TB_D2_FULL + m], b);
+                tc_fence_after();
                 uint32_t a0[32], a1[32];
                 tmem_ld_32x32b_x32(tm_d2 + lane_off + m * 128 + h * 64, a0);
                 tmem_ld_32x32b_x32(tm_d2 + lane_off + m * 128 + h * 64 + 32, a1);
@@ -332,21 +359,21 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                     for (int e = 0; e < 4; ++e) {
                         const int i = j * 8 + e * 2;
                         const float2 res = unpack_act2(ru[e]);
-                        const float v0 = __uint_as_float(i < 32 ? a0[i] : a1[i - 32]) + bias[m] + res.x;
-                        const float v1 = __uint_as_float(i < 32 ? a0[i + 1] : a1[i - 31]) + bias[m] + res.y;
+                        const float v0 = __uint_as_float(i < 32 ? a0[i] : a1[i - 32]) + bias + res.x;
+                        const float v1 = __uint_as_float(i < 32 ? a0[i + 1] : a1[i - 31]) + bias + res.y;
                         ou[e] = pack_act2(v0, v1);
-                        const float2 rd = unpack_act2(ou[e]);
-                        s += rd.x + rd.y;
+                        if (want_sums) {  // ECA squeeze of the next run: sum of what was actually stored
+                            const float2 rd = unpack_act2(ou[e]);
+                            s += rd.x + rd.y;
+                        }
                     }
                     *px = make_uint4(ou[0], ou[1], ou[2], ou[3]);
                 }
-                if (last && p.sums != nullptr) p.sums[static_cast<size_t>(pos) * 384 + m * 128 + r] = s;
-            }
-            tc_fence_before();
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (!last) {
-                if (lane == 0) mbar_arrive(&bars[TB_X_READY]);
+                if (want_sums) p.sums[static_cast<size_t>(pos) * 384 + m * 128 + r] = s;
+                tc_fence_before();
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (!last && lane == 0) mbar_arrive(&bars[TB_X_READY + m]);
             }
         }
         // ---- run output: shared-memory tile -> global (TMA store) ----

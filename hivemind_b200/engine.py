@@ -189,6 +189,13 @@ class Engine:
             raise RuntimeError(_lib.last_error())
         return ms.value, n.value
 
+    def benchResidentMulti(self, iters: int, numWorkers: int):
+        """`iters` fused passes issued round-robin on `numWorkers` worker streams; device ms."""
+        ms, n = C.c_float(), C.c_int()
+        if not self._L.hm_engine_bench_resident_multi(self._h, numWorkers, iters, C.byref(ms), C.byref(n)):
+            raise RuntimeError(_lib.last_error())
+        return ms.value, n.value
+
     def profilePass(self, workerIndex: int = 0):
         arr = (KernelTime * 128)()
         n = C.c_int()

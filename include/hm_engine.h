@@ -188,6 +188,12 @@ int hm_shape_values_half(hm_engine* e, const uint16_t* value, const uint16_t* wd
 int hm_engine_bench_resident(hm_engine* e, size_t worker, int iters, float* ms_total,
                              int* launches_per_pass);
 
+/* The same with `n_workers` execution slots in flight (passes issued round-robin on the
+ * workers' streams, as concurrent search threads do, engine.cc:493-532); elapsed device time
+ * between a fork event and a join event on worker 0's stream. */
+int hm_engine_bench_resident_multi(hm_engine* e, int n_workers, int iters, float* ms_total,
+                                   int* launches_per_pass);
+
 /* Per-kernel timing of one pass with CUDA events between launches: fills up to `cap`
  * entries of (name, ms); returns the count in *n. */
 typedef struct hm_kernel_time {
