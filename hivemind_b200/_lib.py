@@ -51,6 +51,7 @@ SYMBOLS = {
     "hm_policy_indices": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "hm_shape_values_half": (_i, [_vp, _vp, _vp, _vp, _sz, _vp]),
     "hm_engine_bench_resident": (_i, [_vp, _sz, _i, C.POINTER(C.c_float), C.POINTER(_i)]),
+    "hm_engine_trace_trunk": (_i, [_vp, _sz, _i, _vp, C.POINTER(_i)]),
     "hm_engine_bench_resident_multi": (_i, [_vp, _i, _i, C.POINTER(C.c_float), C.POINTER(_i)]),
     "hm_engine_profile_pass": (_i, [_vp, _sz, C.POINTER(KernelTime), _i, C.POINTER(_i)]),
     "hm_engine_debug_fetch": (_i, [_vp, _sz, C.c_char_p, _vp, _sz, C.POINTER(_sz)]),

@@ -475,6 +475,15 @@ int hm_engine_profile_pass(hm_engine* h, size_t worker, hm_kernel_time* out, int
     HM_CATCH(0)
 }
 
+int hm_engine_trace_trunk(hm_engine* h, size_t worker, int run, unsigned long long* out, int* cap) {
+    HM_TRY
+    Worker* w = get_worker(h, worker);
+    if (!w || !use_device(h) || !out) return 0;
+    if (w->pending) { set_error("worker busy"); return 0; }
+    return trace_trunk_run(*w, run, out, cap) ? 1 : 0;
+    HM_CATCH(0)
+}
+
 int hm_engine_debug_fetch(hm_engine* h, size_t worker, const char* name, float* out,
                           size_t cap_floats, size_t* n_floats) {
     HM_TRY

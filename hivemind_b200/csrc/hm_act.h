@@ -19,6 +19,9 @@ __device__ __forceinline__ uint32_t pack_act2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
 }
+__device__ __forceinline__ uint32_t pack_act2_relu(float lo, float hi) {
+    return pack_act2(fmaxf(lo, 0.0f), fmaxf(hi, 0.0f));
+}
 __device__ __forceinline__ float2 unpack_act2(uint32_t u) {
     __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
     return __bfloat1622float2(v);
@@ -32,6 +35,12 @@ __device__ __forceinline__ uint32_t pack_act2(float lo, float hi) {
     // one F2FP.SATFINITE: round to nearest, saturate to +-65504 instead of overflowing to inf
     uint32_t r;
     asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+// max(x, 0) folded into the conversion (F2FP.RELU.SATFINITE)
+__device__ __forceinline__ uint32_t pack_act2_relu(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
     return r;
 }
 __device__ __forceinline__ float2 unpack_act2(uint32_t u) {

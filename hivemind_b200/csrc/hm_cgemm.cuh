@@ -86,40 +86,44 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
     const uint32_t tmem_base = *tmem_slot;
 
     const int kpairs = p.kblocks >> 1;
+    // both single-thread roles run warp-uniform; only the issuing instructions are predicated
     if (warp == 0) {
-        if (lane == 0) {
-            int stage = 0, kcol = 0;
-            uint32_t phase = 1;
-            const int row0 = mb * 128, pos0 = tile * 2;
-            for (int ky = 0; ky < p.ksize; ++ky) {
-                const int sq0 = 8 * (ky - (p.ksize >> 1));   // vertical tap offset as a square shift
-                for (int kx = 0; kx < p.ksize; ++kx) {
-                    for (int kp = 0; kp < kpairs; ++kp, kcol += 128) {
-                        mbar_wait(&empty_bar[stage], phase);
+        const bool leader = elect_one();
+        int stage = 0, kcol = 0;
+        uint32_t phase = 1;
+        const int row0 = mb * 128, pos0 = tile * 2;
+        for (int ky = 0; ky < p.ksize; ++ky) {
+            const int sq0 = 8 * (ky - (p.ksize >> 1));   // vertical tap offset as a square shift
+            for (int kx = 0; kx < p.ksize; ++kx) {
+                for (int kp = 0; kp < kpairs; ++kp, kcol += 128) {
+                    mbar_wait(&empty_bar[stage], phase);
+                    if (leader) {
                         uint8_t* dst = smem + stage * CG_STAGE_BYTES;
                         mbar_arrive_expect_tx(&full_bar[stage], CG_STAGE_BYTES);
                         tma_load_2d(dst, &tmW, &full_bar[stage], kcol, row0);
                         tma_load_2d(dst + 16384, &tmW, &full_bar[stage], kcol + 64, row0);
                         tma_load_3d(dst + 32768, &tmX, &full_bar[stage], sq0, kp * 128, pos0);
                         tma_load_3d(dst + 49152, &tmX, &full_bar[stage], sq0, kp * 128 + 64, pos0);
-                        if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
                     }
+                    __syncwarp();
+                    if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
-            const uint64_t a0 = umma_desc_sw128(smem_u32(smem));
-            const uint64_t b0 = umma_desc_mn_sw128(smem_u32(smem) + 32768, 8192, 1024);
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int ky = 0; ky < p.ksize; ++ky) {
-                for (int kx = 0; kx < p.ksize; ++kx) {       // accumulator = horizontal offset kx
-                    const uint32_t d = tmem_base + kx * 128;
-                    for (int kp = 0; kp < kpairs; ++kp) {
-                        mbar_wait(&full_bar[stage], phase);
-                        tc_fence_after();
+        const bool leader = elect_one();
+        constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
+        const uint64_t a0 = umma_desc_sw128(smem_u32(smem));
+        const uint64_t b0 = umma_desc_mn_sw128(smem_u32(smem) + 32768, 8192, 1024);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int ky = 0; ky < p.ksize; ++ky) {
+            for (int kx = 0; kx < p.ksize; ++kx) {       // accumulator = horizontal offset kx
+                const uint32_t d = tmem_base + kx * 128;
+                for (int kp = 0; kp < kpairs; ++kp) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    if (leader) {
                         const uint32_t so = stage * (CG_STAGE_BYTES / 16);
                         const uint32_t acc0 = (ky | kp) ? 1u : 0u;  // first tile of this accumulator
 #pragma unroll
@@ -130,12 +134,14 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
                                          (j | k) ? 1u : acc0);
                         }
                         umma_commit(&empty_bar[stage]);
-                        if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
                     }
+                    __syncwarp();
+                    if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
                 }
             }
-            umma_commit(accum_bar);
         }
+        if (leader) umma_commit(accum_bar);
+        __syncwarp();
     } else {
         // ===== epilogue: thread = one output channel, both positions =====
         const int q = warp & 3;

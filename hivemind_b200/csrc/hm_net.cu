@@ -326,8 +326,30 @@ static bool kernels_prepare() {
     return ok;
 }
 
+struct TrunkRun {
+    TrunkParams p;
+    CUtensorMap tm_x, tm_w1, tm_w2;
+    int grid;
+};
+bool trace_trunk_run(Worker& w, int run, unsigned long long* out_host, int* cap) {
+    if (run < 0 || run >= static_cast<int>(w.trunk_runs.size())) { set_error("no such trunk run"); return false; }
+    const size_t bytes = 3 * TR_TRACE_CAP * sizeof(unsigned long long);
+    unsigned long long* d = nullptr;
+    if (!cuda_ok(cudaMalloc(&d, bytes), "cudaMalloc(trace)")) return false;
+    cudaMemsetAsync(d, 0, bytes, w.stream);
+    TrunkRun r = *w.trunk_runs[run];
+    r.p.trace = d;
+    if (const char* dbg = getenv("HM_TRUNK_DBG")) r.p.dbg = atoi(dbg);
+    trunk_kernel<<<r.grid, TR_THREADS, TR_SMEM, w.stream>>>(r.p, r.tm_x, r.tm_w1, r.tm_w2);
+    bool ok = cuda_ok(cudaMemcpyAsync(out_host, d, bytes, cudaMemcpyDeviceToHost, w.stream), "D2H trace") &&
+              cuda_ok(cudaStreamSynchronize(w.stream), "trace sync");
+    cudaFree(d);
+    if (cap) *cap = TR_TRACE_CAP;
+    return ok;
+}
+
 // A run of consecutive bottleneck blocks [first, last) as one trunk_kernel launch.
-static bool add_trunk_run(std::vector<Op>& ops, const Net& net, int first, int last, act_t* x,
+static bool add_trunk_run(Worker& w, std::vector<Op>& ops, const Net& net, int first, int last, act_t* x,
                           const float* gate, float* sums, int n_pos) {
     if (last - first > TR_MAX_BLOCKS) { set_error("trunk run too long"); return false; }
     CUtensorMap tm_x;
@@ -344,8 +366,11 @@ static bool add_trunk_run(std::vector<Op>& ops, const Net& net, int first, int l
     p.bias2 = net.trunk_bias2;
     p.gate = gate;
     p.sums = sums;
+    p.trace = nullptr;
+    p.dbg = 0;
     const int grid = n_pos / 2;
     const CUtensorMap tw1 = net.tm_w1, tw2 = net.tm_w2;
+    w.trunk_runs.push_back(std::make_shared<TrunkRun>(TrunkRun{p, tm_x, tw1, tw2, grid}));
     Op op;
     op.name = "trunk.b" + std::to_string(first) + "-" + std::to_string(last - 1) + (gate ? "+eca" : "");
     op.klass = "dense";
@@ -449,7 +474,7 @@ static bool setup_worker(Engine* e, Worker& w) {
             gate = w.d_gate;
         }
         float* sums = (last < nblk && net.blocks[last].eca) ? w.d_sums : nullptr;
-        if (!add_trunk_run(ops, net, first, last, w.d_trunk, gate, sums, B)) return false;
+        if (!add_trunk_run(w, ops, net, first, last, w.d_trunk, gate, sums, B)) return false;
         first = last;
     }
     w.debug_views["planes"] = {w.d_planes, {B, HM_NB_INPUT_VALUES, 0}};

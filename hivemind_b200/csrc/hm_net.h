@@ -89,6 +89,7 @@ struct Op {
     std::function<void(cudaStream_t)> launch;
 };
 
+struct TrunkRun;  // hm_net.cu (parameters of one trunk_kernel launch, kept for tracing)
 struct Worker {
     int batch = 0;        // positions per request (even)
     size_t move_cap = 0;
@@ -131,7 +132,10 @@ struct Worker {
     std::map<std::string, std::pair<const void*, std::vector<int>>> debug_views;  // name -> (ptr, {rows, cols, is_f32})
     std::vector<void*> dev_allocs, host_allocs;
     std::vector<cudaEvent_t> events;
+    std::vector<std::shared_ptr<TrunkRun>> trunk_runs;
 };
+// bring-up aid: launch trunk run `run` of `w` once with timeline tracing; out = 3 roles x cap
+bool trace_trunk_run(Worker& w, int run, unsigned long long* out_host, int* cap);
 
 struct Engine {
     int device = 0, batch = 0, n_workers = 0;

@@ -44,7 +44,20 @@ struct TrunkParams {
     const float* bias2;  // [...][384]
     const float* gate;   // [pos][384] ECA gate of the run's first block, or nullptr
     float* sums;         // [pos][384] channel sums (over 64 squares) of the run's output, or nullptr
+    unsigned long long* trace;  // bring-up aid: CTA 0 logs (tag << 48 | clock) per role, or nullptr
+    int dbg;                    // bring-up aid (timing experiments only, results are wrong when set):
+                                // bit0 skip depthwise math, bit1 skip TMEM drain, bit2 skip Z store,
+                                // bit3 / bit4 skip the math only on sub-partitions 0,1 / 2,3
 };
+
+// timeline tracing (tools/trace_trunk.py): roles 0 = producer, 1 = MMA issuer, 2 = compute warp 2
+constexpr int TR_TRACE_CAP = 2048;
+#define TR_MARK(role, tag)                                                                       \
+    do {                                                                                         \
+        if (tr_trace != nullptr && trace_n < TR_TRACE_CAP)                                       \
+            tr_trace[(role) * TR_TRACE_CAP + trace_n++] =                                        \
+                (static_cast<unsigned long long>(tag) << 48) | (clock64() & 0xffffffffffffull);  \
+    } while (0)
 
 constexpr int TR_THREADS = 320;
 constexpr int TR_COMPUTE = 256;
@@ -101,51 +114,97 @@ __device__ __forceinline__ void dw_board(const float (&y)[64], const float (&w)[
                     acc = fmaf(y[yy * 8 + xx], w[ky * KS + kx], acc);
                 }
             }
-            o[xo] = fmaxf(acc, 0.0f);
+            o[xo] = acc;
         }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) packed[yo * 4 + j] = pack_act2(o[2 * j], o[2 * j + 1]);
+        for (int j = 0; j < 4; ++j) packed[yo * 4 + j] = pack_act2_relu(o[2 * j], o[2 * j + 1]);
     }
 }
 
+// Per-thread parameters of one 128-channel chunk: pw1 bias, depthwise bias, k*k depthwise taps.
 template <int KS>
-__device__ __forceinline__ void trunk_chunk(const float* __restrict__ par, int r, uint32_t tm_d1,
-                                            uint64_t* bars, uint32_t d1_n, uint32_t z_n,
-                                            uint8_t* zrow, int lane) {
-    // parameters of this thread's channel (issued before the wait so they are in flight)
+struct ChunkPar {
     float w[KS * KS];
+    float b1, bd;
+    __device__ __forceinline__ void load(const float* __restrict__ par, int r) {
 #pragma unroll
-    for (int t = 0; t < KS * KS; ++t) w[t] = __ldg(par + 256 + t * 128 + r);
-    const float b1 = __ldg(par + r);
-    const float bd = __ldg(par + 128 + r);
+        for (int t = 0; t < KS * KS; ++t) w[t] = __ldg(par + 256 + t * 128 + r);
+        b1 = __ldg(par + r);
+        bd = __ldg(par + 128 + r);
+    }
+};
+
+// One chunk on the compute warps.  `cur` holds this chunk's parameters (already in registers);
+// the next chunk's parameters are requested while this chunk's depthwise math runs, so their
+// L2 latency never sits between "D1 is full" and the first use.
+template <int KS>
+__device__ __forceinline__ void trunk_chunk(ChunkPar<KS>& cur, const float* __restrict__ par_next,
+                                            int r, uint32_t tm_d1, uint64_t* bars, uint32_t d1_n,
+                                            uint32_t z_n, uint8_t* zrow, int lane,
+                                            unsigned long long* tr_trace, int& trace_n, int dbg) {
     float y[64];
+    TR_MARK(2, 1);
     tr_wait_full(&bars[TB_D1_FULL], d1_n);
     tc_fence_after();
-    {
+    TR_MARK(2, 2);
+    if (dbg & 2) {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) y[j] = cur.b1;
+    } else {
         uint32_t a0[32], a1[32];
         tmem_ld_32x32b_x32(tm_d1, a0);
         tmem_ld_32x32b_x32(tm_d1 + 32, a1);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-            y[j] = fmaxf(__uint_as_float(a0[j]) + b1, 0.0f);
-            y[32 + j] = fmaxf(__uint_as_float(a1[j]) + b1, 0.0f);
+            y[j] = fmaxf(__uint_as_float(a0[j]) + cur.b1, 0.0f);
+            y[32 + j] = fmaxf(__uint_as_float(a1[j]) + cur.b1, 0.0f);
         }
     }
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(&bars[TB_D1_EMPTY]);  // D1 is free as soon as it is in registers
+    TR_MARK(2, 3);
+    ChunkPar<KS> nxt;
+    if (par_next != nullptr) nxt.load(par_next, r);
     uint32_t packed[32];
-    dw_board<KS>(y, w, bd, packed);
-    tr_wait_empty(&bars[TB_Z_EMPTY], z_n);  // pw2 of the previous chunk has consumed Z
-    const int key = r & 7;
+    if ((dbg & 1) || ((dbg & 8) && ((threadIdx.x >> 5) & 3) < 2) || ((dbg & 16) && ((threadIdx.x >> 5) & 3) >= 2)) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-        *reinterpret_cast<uint4*>(zrow + ((j ^ key) << 4)) =
-            make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
-    fence_proxy_async_smem();
+        for (int j = 0; j < 32; ++j) packed[j] = __float_as_uint(y[2 * j]);
+    } else {
+        dw_board<KS>(y, cur.w, cur.bd, packed);
+    }
+    TR_MARK(2, 4);
+    tr_wait_empty(&bars[TB_Z_EMPTY], z_n);  // pw2 of the previous chunk has consumed Z
+    TR_MARK(2, 5);
+    const int key = r & 7;
+    if (!(dbg & 4)) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(zrow + ((j ^ key) << 4)) =
+                make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+        fence_proxy_async_smem();
+    }
     __syncwarp();
     if (lane == 0) mbar_arrive(&bars[TB_Z_FULL]);
+    TR_MARK(2, 6);
+    if (par_next != nullptr) cur = nxt;
+}
+
+// all chunks of one bottleneck block
+template <int KS>
+__device__ __forceinline__ void trunk_block_chunks(const float* __restrict__ par0, int nch, int r,
+                                                   uint32_t tm_d1, uint64_t* bars, uint32_t& d1_n,
+                                                   uint32_t& z_n, uint8_t* zrow, int lane,
+                                                   unsigned long long* tr_trace, int& trace_n, int dbg) {
+    ChunkPar<KS> cur;
+    cur.load(par0, r);
+    for (int c = 0; c < nch; ++c) {
+        const float* nxt = (c + 1 < nch) ? par0 + static_cast<size_t>(c + 1) * TR_PAR_FLOATS : nullptr;
+        trunk_chunk<KS>(cur, nxt, r, tm_d1, bars, d1_n, z_n, zrow, lane, tr_trace, trace_n, dbg);
+        ++d1_n;
+        ++z_n;
+    }
 }
 
 __global__ void __launch_bounds__(TR_THREADS, 1)
@@ -159,6 +218,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x;
+    unsigned long long* const tr_trace = (blockIdx.x == 0 && (lane == 0)) ? p.trace : nullptr;
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmX);
@@ -182,64 +242,87 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
     const uint32_t tm_d2 = tmem_base;
     const uint32_t tm_d1 = tmem_base + 384u;
 
+    // The two single-thread roles run with ALL 32 lanes in uniform control flow (waits, loop
+    // counters, descriptor arithmetic stay warp-uniform -> uniform registers, no per-lane
+    // election loops around every UTMALDG / UTCHMMA); only the issuing instructions themselves
+    // are predicated on one elected lane.
     if (warp == 0) {
         // ================================ TMA producer ================================
-        if (lane == 0) {
+        const bool leader = elect_one();
+        if (leader) {
             mbar_arrive_expect_tx(&bars[TB_X_FULL], 6 * 16384);
+#pragma unroll
             for (int kb = 0; kb < 6; ++kb)
                 tma_load_3d(smem + TR_X_OFF + kb * 16384, &tmX, &bars[TB_X_FULL], 0, kb * 64, tile * 2);
-            // one group = 6 tiles = one lap over the ring; `par` is the empty-barrier parity of the lap
-            uint32_t par = 1;
-            auto group_w1 = [&](int g) {   // W1 rows [g*128, +128) x K blocks 0..5
+        }
+        __syncwarp();
+        // one group = 6 tiles = one lap over the ring; `par` is the empty-barrier parity of the lap
+        uint32_t par = 1;
+        int trace_n = 0;
+        auto group_w1 = [&](int g) {   // W1 rows [g*128, +128) x K blocks 0..5
+            TR_MARK(0, 1);
 #pragma unroll
-                for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
-                    mbar_wait(&bars[TB_PAIR_EMPTY + b2], par);
+            for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
+                mbar_wait(&bars[TB_PAIR_EMPTY + b2], par);
+                TR_MARK(0, 10 + b2);
+                if (leader) {
                     mbar_arrive_expect_tx(&bars[TB_PAIR_FULL + b2], 2 * TR_SLOT_BYTES);
 #pragma unroll
                     for (int j = 0; j < 2; ++j)
                         tma_load_2d(smem + TR_RING_OFF + (2 * b2 + j) * TR_SLOT_BYTES, &tmW1,
                                     &bars[TB_PAIR_FULL + b2], (2 * b2 + j) * 64, g * 128);
                 }
-                par ^= 1;
-            };
-            auto group_w2 = [&](int g) {   // W2 of chunk g: tile s = m*2 + kh -> rows g*384 + m*128, K half kh
+                __syncwarp();
+            }
+            par ^= 1;
+        };
+        auto group_w2 = [&](int g) {   // W2 of chunk g: tile s = m*2 + kh -> rows g*384 + m*128, K half kh
+            TR_MARK(0, 2);
 #pragma unroll
-                for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
-                    mbar_wait(&bars[TB_PAIR_EMPTY + b2], par);
+            for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
+                mbar_wait(&bars[TB_PAIR_EMPTY + b2], par);
+                TR_MARK(0, 20 + b2);
+                if (leader) {
                     mbar_arrive_expect_tx(&bars[TB_PAIR_FULL + b2], 2 * TR_SLOT_BYTES);
 #pragma unroll
                     for (int j = 0; j < 2; ++j)   // pair b2 = output block m = b2, K halves kh = j
                         tma_load_2d(smem + TR_RING_OFF + (2 * b2 + j) * TR_SLOT_BYTES, &tmW2,
                                     &bars[TB_PAIR_FULL + b2], j * 64, g * 384 + b2 * 128);
                 }
-                par ^= 1;
-            };
-            for (int b = 0; b < p.n_blocks; ++b) {
-                const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks;
-                group_w1(g0);
-                for (int c = 0; c < nch; ++c) {
-                    if (c + 1 < nch) group_w1(g0 + c + 1);
-                    group_w2(g0 + c);
-                }
+                __syncwarp();
+            }
+            par ^= 1;
+        };
+        for (int b = 0; b < p.n_blocks; ++b) {
+            const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks;
+            group_w1(g0);
+            for (int c = 0; c < nch; ++c) {
+                if (c + 1 < nch) group_w1(g0 + c + 1);
+                group_w2(g0 + c);
             }
         }
     } else if (warp == 1) {
         // ================================ MMA issuer ================================
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
-            uint32_t d1_n = 0, z_n = 0, par = 0;
-            // descriptors differ only in the start-address field (16-byte units): hoist the bases
-            const uint64_t a0 = umma_desc_sw128(smem_u32(smem + TR_RING_OFF));
-            const uint64_t xd0 = umma_desc_mn_sw128(smem_u32(smem + TR_X_OFF), 8192, 1024);
-            const uint64_t zd0 = umma_desc_mn_sw128(smem_u32(smem + TR_Z_OFF), 8192, 1024);
-            auto pw1 = [&](int xblock) {   // xblock >= 0: first pw1 of bottleneck block `xblock`
-                tr_wait_empty(&bars[TB_D1_EMPTY], d1_n);
-                tc_fence_after();
+        const bool leader = elect_one();
+        constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
+        uint32_t d1_n = 0, z_n = 0, par = 0;
+        int trace_n = 0;
+        // descriptors differ only in the start-address field (16-byte units): hoist the bases
+        const uint64_t a0 = umma_desc_sw128(smem_u32(smem + TR_RING_OFF));
+        const uint64_t xd0 = umma_desc_mn_sw128(smem_u32(smem + TR_X_OFF), 8192, 1024);
+        const uint64_t zd0 = umma_desc_mn_sw128(smem_u32(smem + TR_Z_OFF), 8192, 1024);
+        auto pw1 = [&](int xblock) {   // xblock >= 0: first pw1 of bottleneck block `xblock`
+            TR_MARK(1, 1);
+            tr_wait_empty(&bars[TB_D1_EMPTY], d1_n);
+            tc_fence_after();
+            TR_MARK(1, 2);
 #pragma unroll
-                for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
-                    if (xblock >= 0) tr_wait_full(&bars[TB_X_READY + b2], xblock);  // X blocks 2*b2, 2*b2+1 ready
-                    mbar_wait(&bars[TB_PAIR_FULL + b2], par);
-                    tc_fence_after();
+            for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
+                if (xblock >= 0) tr_wait_full(&bars[TB_X_READY + b2], xblock);  // X blocks 2*b2, 2*b2+1 ready
+                mbar_wait(&bars[TB_PAIR_FULL + b2], par);
+                tc_fence_after();
+                TR_MARK(1, 10 + b2);
+                if (leader) {
 #pragma unroll
                     for (int j = 0; j < 2; ++j) {
                         const int kb = 2 * b2 + j;  // ring slot = K block of X
@@ -249,23 +332,31 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                                      (kb | k) ? 1u : 0u);
                     }
                     umma_commit(&bars[TB_PAIR_EMPTY + b2]);
+                    if (b2 == TR_PAIRS - 1) umma_commit(&bars[TB_D1_FULL]);
                 }
-                par ^= 1;
-                umma_commit(&bars[TB_D1_FULL]);
-                ++d1_n;
-            };
-            for (int b = 0; b < p.n_blocks; ++b) {
-                const int nch = p.blk[b].n_chunks;
-                pw1(b);
-                for (int c = 0; c < nch; ++c) {
-                    if (c + 1 < nch) pw1(-1);
-                    tr_wait_full(&bars[TB_Z_FULL], z_n);
-                    tc_fence_after();
-                    const uint32_t acc0 = c > 0 ? 1u : 0u;
+                __syncwarp();
+            }
+            par ^= 1;
+            ++d1_n;
+            TR_MARK(1, 3);
+        };
+        for (int b = 0; b < p.n_blocks; ++b) {
+            const int nch = p.blk[b].n_chunks;
+            pw1(b);
+            for (int c = 0; c < nch; ++c) {
+                if (c + 1 < nch) pw1(-1);
+                TR_MARK(1, 4);
+                tr_wait_full(&bars[TB_Z_FULL], z_n);
+                tc_fence_after();
+                TR_MARK(1, 5);
+                const uint32_t acc0 = c > 0 ? 1u : 0u;
+                const bool last_chunk = c + 1 == nch;
 #pragma unroll
-                    for (int m = 0; m < TR_PAIRS; ++m) {   // pair = output channel block m
-                        mbar_wait(&bars[TB_PAIR_FULL + m], par);
-                        tc_fence_after();
+                for (int m = 0; m < TR_PAIRS; ++m) {   // pair = output channel block m
+                    mbar_wait(&bars[TB_PAIR_FULL + m], par);
+                    tc_fence_after();
+                    TR_MARK(1, 20 + m);
+                    if (leader) {
 #pragma unroll
                         for (int kh = 0; kh < 2; ++kh) {
 #pragma unroll
@@ -274,12 +365,14 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                                          zd0 + (kh * 1024 + k * 128), idesc, (kh | k) ? 1u : acc0);
                         }
                         umma_commit(&bars[TB_PAIR_EMPTY + m]);
-                        if (c + 1 == nch) umma_commit(&bars[TB_D2_FULL + m]);  // output block m complete
+                        if (last_chunk) umma_commit(&bars[TB_D2_FULL + m]);  // output block m complete
+                        if (m == TR_PAIRS - 1) umma_commit(&bars[TB_Z_EMPTY]);
                     }
-                    par ^= 1;
-                    umma_commit(&bars[TB_Z_EMPTY]);
-                    ++z_n;
+                    __syncwarp();
                 }
+                par ^= 1;
+                ++z_n;
+                TR_MARK(1, 6);
             }
         }
     } else {
@@ -322,17 +415,17 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         }
 
         uint32_t d1_n = 0, z_n = 0;
+        int trace_n = 0;
+        unsigned long long* const ctrace = warp == 2 ? tr_trace : nullptr;
         for (int b = 0; b < p.n_blocks; ++b) {
             const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks, ks = p.blk[b].ksize;
-            for (int c = 0; c < nch; ++c) {
-                const float* par = p.par + static_cast<size_t>(g0 + c) * TR_PAR_FLOATS;
+            {
+                const float* par0 = p.par + static_cast<size_t>(g0) * TR_PAR_FLOATS;
                 uint8_t* zrow = smem + TR_Z_OFF + row_off;
                 if (ks == 3)
-                    trunk_chunk<3>(par, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane);
+                    trunk_block_chunks<3>(par0, nch, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane, ctrace, trace_n, p.dbg);
                 else
-                    trunk_chunk<5>(par, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane);
-                ++d1_n;
-                ++z_n;
+                    trunk_block_chunks<5>(par0, nch, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane, ctrace, trace_n, p.dbg);
             }
             // ---- block epilogue: x <- x + D2 + b2, in place in shared memory ----
             const bool last = (b + 1 == p.n_blocks);
@@ -341,8 +434,10 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
 #pragma unroll 1
             for (int m = 0; m < 3; ++m) {
                 const float bias = __ldg(b2 + m * 128 + r);
+                { unsigned long long* tr_trace = ctrace; TR_MARK(2, 7); }
                 tr_wait_full(&bars[TB_D2_FULL + m], b);
                 tc_fence_after();
+                { unsigned long long* tr_trace = ctrace; TR_MARK(2, 8); }
                 uint32_t a0[32], a1[32];
                 tmem_ld_32x32b_x32(tm_d2 + lane_off + m * 128 + h * 64, a0);
                 tmem_ld_32x32b_x32(tm_d2 + lane_off + m * 128 + h * 64 + 32, a1);
@@ -374,6 +469,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (!last && lane == 0) mbar_arrive(&bars[TB_X_READY + m]);
+                { unsigned long long* tr_trace = ctrace; TR_MARK(2, 9); }
             }
         }
         // ---- run output: shared-memory tile -> global (TMA store) ----

@@ -196,6 +196,19 @@ class Engine:
             raise RuntimeError(_lib.last_error())
         return ms.value, n.value
 
+    def traceTrunk(self, run: int, workerIndex: int = 0):
+        """Timeline of trunk run `run` (CTA 0): dict role -> list of (tag, clock)."""
+        buf = np.zeros(3 * 2048, np.uint64)
+        cap = C.c_int()
+        if not self._L.hm_engine_trace_trunk(self._h, workerIndex, run, buf.ctypes.data, C.byref(cap)):
+            raise RuntimeError(_lib.last_error())
+        out = {}
+        for role in range(3):
+            ev = buf[role * cap.value:(role + 1) * cap.value]
+            ev = ev[ev != 0]
+            out[role] = [(int(e >> np.uint64(48)), int(e & np.uint64(0xFFFFFFFFFFFF))) for e in ev]
+        return out
+
     def profilePass(self, workerIndex: int = 0):
         arr = (KernelTime * 128)()
         n = C.c_int()

@@ -205,6 +205,11 @@ typedef struct hm_kernel_time {
 int hm_engine_profile_pass(hm_engine* e, size_t worker, hm_kernel_time* out, int cap,
                            int* n);
 
+/* Debug: launch trunk run `run` of the layer program once with timeline tracing: CTA 0 logs
+ * (tag << 48 | SM clock) events of its TMA producer, MMA issuer and first compute warp.
+ * out = 3 roles x *cap entries (pass room for 3 x 2048); unused entries are 0. */
+int hm_engine_trace_trunk(hm_engine* e, size_t worker, int run, unsigned long long* out, int* cap);
+
 /* Debug: copy an intermediate activation of the last pass on `worker` to host as fp32.
  * name in {"planes","stem","block<i>","trunk","value_feat","policy_shared"}. */
 int hm_engine_debug_fetch(hm_engine* e, size_t worker, const char* name, float* out,

@@ -79,7 +79,8 @@ __global__ void __launch_bounds__(128, 1) mmaring(const __grid_constant__ CUtens
 // B descriptors are hoisted, only the low descriptor word is recomputed with one 32-bit add.
 template <int SLOTS, int GROUP>
 __global__ void __launch_bounds__(128, 1) mmaring_fast(const __grid_constant__ CUtensorMap tm, int n_laps, int rows_total,
-                                                       long long* cycles_out) {
+                                                       long long* cycles_out, int stagger, int mode,
+                                                       const __grid_constant__ CUtensorMap tm2, const uint8_t* flat) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* bop = smem;
     uint8_t* ringp = smem + 16384;
@@ -101,16 +102,23 @@ __global__ void __launch_bounds__(128, 1) mmaring_fast(const __grid_constant__ C
     const uint32_t tmem = *slot;
     long long t0 = clock64();
     if (warp == 0 && lane == 0) {
-        int rb = (blockIdx.x * 7) % (rows_total / 128);
+        int rb = stagger ? (blockIdx.x * 7) % (rows_total / 128) : 0;
         uint32_t par = 1;
         for (int lap = 0; lap < n_laps; ++lap) {
 #pragma unroll
             for (int b = 0; b < NB; ++b) {
                 mbar_wait(&empty[b], par);
                 mbar_arrive_expect_tx(&full[b], 16384 * GROUP);
+                if (mode == 2) {
+                    bulk_load_1d(ringp + b * GROUP * 16384, flat + ((size_t)rb * 6 + b * GROUP) * 16384, 16384 * GROUP, &full[b]);
+                } else {
 #pragma unroll
-                for (int j = 0; j < GROUP; ++j)
-                    tma_load_2d(ringp + (b * GROUP + j) * 16384, &tm, &full[b], ((b * GROUP + j) % 6) * 64, rb * 128);
+                    for (int j = 0; j < GROUP; ++j) {
+                        const int s = b * GROUP + j;
+                        if (mode == 1) tma_load_2d(ringp + s * 16384, &tm2, &full[b], (s & 1) * 64, (rb * 3 + (s >> 1)) * 128);
+                        else tma_load_2d(ringp + s * 16384, &tm, &full[b], (s % 6) * 64, rb * 128);
+                    }
+                }
             }
             par ^= 1;
             rb = rb + 1 == rows_total / 128 ? 0 : rb + 1;
@@ -144,20 +152,22 @@ __global__ void __launch_bounds__(128, 1) mmaring_fast(const __grid_constant__ C
     __syncthreads();
     if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 128); }
 }
+static CUtensorMap g_tm2;
+static const uint8_t* g_flat;
 template <int SLOTS, int GROUP>
 static void run_fast(const CUtensorMap& tm, int rows, long long* dc) {
     cudaFuncSetAttribute(mmaring_fast<SLOTS, GROUP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 13 * 16384 + 1024);
     const int n_laps = 2400 / SLOTS;
-    for (int grid : {1, 148}) {
+    for (int mode : {0, 1, 2}) for (int stagger : {0}) for (int grid : {148}) {
         for (int rep = 0; rep < 2; ++rep) {
-            mmaring_fast<SLOTS, GROUP><<<grid, 128, (SLOTS + 1) * 16384 + 1024>>>(tm, n_laps, rows, dc);
+            mmaring_fast<SLOTS, GROUP><<<grid, 128, (SLOTS + 1) * 16384 + 1024>>>(tm, n_laps, rows, dc, stagger, mode, g_tm2, g_flat);
             cudaError_t e = cudaDeviceSynchronize();
             if (e != cudaSuccess) { printf("err %s\n", cudaGetErrorString(e)); exit(1); }
         }
         std::vector<long long> c(grid);
         cudaMemcpy(c.data(), dc, grid * 8, cudaMemcpyDeviceToHost);
         double mx = 0; for (auto v : c) if (v > mx) mx = v;
-        printf("fast %4d %5d %5d  %10.1f\n", grid, SLOTS, GROUP, mx / (n_laps * SLOTS));
+        printf("fast mode=%d %4d %5d %5d  %10.1f\n", mode, grid, SLOTS, GROUP, mx / (n_laps * SLOTS));
     }
 }
 
@@ -174,12 +184,20 @@ int main() {
     CUresult r = cuTensorMapEncodeTiled(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, d, dims, strides, box, es,
         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r) { printf("encode %d\n", (int)r); return 1; }
+    {   // W2-like view of the same memory: [rows*3][128] fp16, 256-byte pitch
+        cuuint64_t d2[2] = {128, (cuuint64_t)rows * 3};
+        cuuint64_t s2[1] = {256};
+        r = cuTensorMapEncodeTiled(&g_tm2, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, d, d2, s2, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r) { printf("encode2 %d\n", (int)r); return 1; }
+        g_flat = reinterpret_cast<const uint8_t*>(d);
+    }
     long long* dc;
     cudaMalloc(&dc, 1024 * 8);
     cudaFuncSetAttribute(mmaring, cudaFuncAttributeMaxDynamicSharedMemorySize, 13 * 16384 + 1024);
     const int n_stages = 2400;
     printf("mma grid slots group  cycles/stage (tensor floor 256)\n");
-    for (int do_mma : {1}) for (int grid : {148}) for (int group : {1, 2}) for (int slots : {4, 12}) {
+    for (int do_mma : {1}) for (int grid : {148}) for (int group : {2}) for (int slots : {4}) {
         if (slots % group || slots / group < 2) continue;
         for (int rep = 0; rep < 2; ++rep) {
             mmaring<<<grid, 128, (slots + 1) * 16384 + 1024>>>(tm, slots, group, n_stages, rows, do_mma, dc);
@@ -191,11 +209,8 @@ int main() {
         double mx = 0; for (auto v : c) if (v > mx) mx = v;
         printf("%3d %4d %5d %5d  %10.1f\n", do_mma, grid, slots, group, mx / n_stages);
     }
-    run_fast<4, 1>(tm, rows, dc);
-    run_fast<6, 1>(tm, rows, dc);
     run_fast<6, 2>(tm, rows, dc);
     run_fast<6, 3>(tm, rows, dc);
-    run_fast<12, 2>(tm, rows, dc);
-    run_fast<12, 4>(tm, rows, dc);
+    run_fast<8, 2>(tm, rows, dc);
     return 0;
 }
