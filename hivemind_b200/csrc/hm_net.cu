@@ -236,6 +236,18 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
             blk.eca_b = upload(*net, std::vector<float>(eb->data, eb->data + 384));
             if (!blk.eca_wt || !blk.eca_b) return nullptr;
             net->param_count += ew->numel() + eb->numel();
+            // in-kernel ECA (hm_trunk.cuh): Wc [384 out][384 in] rides in W1cat as 3 extra row
+            // chunks (same [rows][384] K-major shape as W1), its bias in the bias2 array
+            blk.eca_chunk0 = net->total_chunks;
+            net->total_chunks += 3;
+            w1cat.resize(static_cast<size_t>(net->total_chunks) * 128 * 384, float_to_act(0.0f));
+            w2cat.resize(static_cast<size_t>(net->total_chunks) * 384 * 128, float_to_act(0.0f));
+            par.resize(static_cast<size_t>(net->total_chunks) * 27 * 128, 0.0f);
+            for (int o = 0; o < 384; ++o)
+                for (int k = 0; k < 384; ++k)
+                    w1cat[(static_cast<size_t>(blk.eca_chunk0) * 128 + o) * 384 + k] = float_to_act(ew->data[o * 384 + k]);
+            blk.eca_bias_off = static_cast<int>(bias2.size());
+            bias2.insert(bias2.end(), eb->data, eb->data + 384);
         }
         net->blocks.push_back(blk);
     }
@@ -359,7 +371,8 @@ static bool add_trunk_run(Worker& w, std::vector<Op>& ops, const Net& net, int f
     double macs = 0;
     for (int i = first; i < last; ++i) {
         const Block& b = net.blocks[i];
-        p.blk[i - first] = TrunkBlock{b.chunk0, b.n_chunks, b.ksize, b.bias2_off};
+        p.blk[i - first] = TrunkBlock{b.chunk0, b.n_chunks, b.ksize, b.bias2_off,
+                                      b.eca ? b.eca_chunk0 : -1, b.eca_bias_off};
         macs += b.macs_per_pos();
     }
     p.par = net.trunk_par;
@@ -372,7 +385,7 @@ static bool add_trunk_run(Worker& w, std::vector<Op>& ops, const Net& net, int f
     const CUtensorMap tw1 = net.tm_w1, tw2 = net.tm_w2;
     w.trunk_runs.push_back(std::make_shared<TrunkRun>(TrunkRun{p, tm_x, tw1, tw2, grid}));
     Op op;
-    op.name = "trunk.b" + std::to_string(first) + "-" + std::to_string(last - 1) + (gate ? "+eca" : "");
+    op.name = "trunk.b" + std::to_string(first) + "-" + std::to_string(last - 1);
     op.klass = "dense";
     op.flops = 2.0 * macs * n_pos;
     op.bytes = 2.0 * n_pos * 64 * 384 * 2;
@@ -452,11 +465,12 @@ static bool setup_worker(Engine* e, Worker& w) {
     int nblk = static_cast<int>(net.blocks.size());
     if (const char* stop = getenv("HM_TRUNK_STOP"))  // debugging aid (tools/diagnose.py): truncate the trunk
         nblk = std::max(0, std::min(nblk, atoi(stop)));
-    // runs of blocks are cut where an ECA gate needs the complete previous output
-    // (builder_util.py:77-80: the gate is a function of ALL channel means of the block input)
+    // the whole trunk is one launch: ECA gates inside a run are computed in the kernel (a gate
+    // depends on the channel means of the SAME position only, builder_util.py:77-80); a run
+    // longer than TR_MAX_BLOCKS would be cut, with the gate of its first block from eca_gate_kernel
     for (int first = 0; first < nblk;) {
         int last = first + 1;
-        while (last < nblk && !net.blocks[last].eca && last - first < TR_MAX_BLOCKS) ++last;
+        while (last < nblk && last - first < TR_MAX_BLOCKS) ++last;
         const Block& b0 = net.blocks[first];
         const float* gate = nullptr;
         if (b0.eca) {

@@ -53,6 +53,8 @@ struct Block {                 // one bottleneck block inside the trunk kernel (
     bool eca = false;
     int chunk0 = 0, n_chunks = 0;  // 128-channel chunks in W1cat / W2cat / par
     int bias2_off = 0;             // offset into Net::trunk_bias2
+    int eca_chunk0 = -1;           // row chunk of the ECA weight inside W1cat (in-kernel ECA)
+    int eca_bias_off = 0;          // offset of the ECA bias inside Net::trunk_bias2
     act_t* eca_wt = nullptr;       // [384 in][384 out]
     float* eca_b = nullptr;
     double macs_per_pos() const { return 2.0 * 64.0 * 384.0 * cop; }

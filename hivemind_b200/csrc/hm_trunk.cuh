@@ -36,6 +36,8 @@ struct TrunkBlock {
     int n_chunks;  // ceil(cop / 128)
     int ksize;     // 3 or 5
     int bias2_off; // offset into bias2 (floats)
+    int eca_chunk0;   // ECA on the block input: first of 3 row chunks of Wc in W1cat, or -1
+    int eca_bias_off; // offset of the 384 ECA biases in bias2
 };
 struct TrunkParams {
     int n_blocks;
@@ -84,7 +86,8 @@ enum {
     TB_D2_FULL = TB_X_READY + 3,              // 3
     TB_PAIR_FULL = TB_D2_FULL + 3,            // TR_PAIRS
     TB_PAIR_EMPTY = TB_PAIR_FULL + TR_PAIRS,  // TR_PAIRS
-    TB_COUNT = TB_PAIR_EMPTY + TR_PAIRS
+    TB_ECA_DONE = TB_PAIR_EMPTY + TR_PAIRS,   // TR_PAIRS: compute warps finished reading a Wc tile pair
+    TB_COUNT = TB_ECA_DONE + TR_PAIRS
 };
 
 // k-th completion (k = 0, 1, ...) of a "full"-type barrier
@@ -226,7 +229,9 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         tma_prefetch_desc(&tmW2);
         for (int i = 0; i < TB_COUNT; ++i) {
             uint32_t count = 1;
-            if ((i >= TB_X_READY && i < TB_X_READY + 3) || i == TB_D1_EMPTY || i == TB_Z_FULL) count = 8;
+            if ((i >= TB_X_READY && i < TB_X_READY + 3) || i == TB_D1_EMPTY || i == TB_Z_FULL ||
+                (i >= TB_ECA_DONE && i < TB_ECA_DONE + TR_PAIRS))
+                count = 8;
             mbar_init(&bars[i], count);
         }
         fence_barrier_init();
@@ -295,6 +300,8 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         };
         for (int b = 0; b < p.n_blocks; ++b) {
             const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks;
+            if (b > 0 && p.blk[b].eca_chunk0 >= 0)   // in-kernel ECA: Wc streams through the ring like W1
+                for (int m = 0; m < 3; ++m) group_w1(p.blk[b].eca_chunk0 + m);
             group_w1(g0);
             for (int c = 0; c < nch; ++c) {
                 if (c + 1 < nch) group_w1(g0 + c + 1);
@@ -308,9 +315,12 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         uint32_t d1_n = 0, z_n = 0, par = 0;
         int trace_n = 0;
         // descriptors differ only in the start-address field (16-byte units): hoist the bases
-        const uint64_t a0 = umma_desc_sw128(smem_u32(smem + TR_RING_OFF));
-        const uint64_t xd0 = umma_desc_mn_sw128(smem_u32(smem + TR_X_OFF), 8192, 1024);
-        const uint64_t zd0 = umma_desc_mn_sw128(smem_u32(smem + TR_Z_OFF), 8192, 1024);
+        const uint64_t a0d = umma_desc_sw128(smem_u32(smem + TR_RING_OFF));
+        const uint64_t xd0d = umma_desc_mn_sw128(smem_u32(smem + TR_X_OFF), 8192, 1024);
+        const uint64_t zd0d = umma_desc_mn_sw128(smem_u32(smem + TR_Z_OFF), 8192, 1024);
+        const uint32_t a0 = static_cast<uint32_t>(a0d), a_hi = static_cast<uint32_t>(a0d >> 32);
+        const uint32_t xd0 = static_cast<uint32_t>(xd0d), zd0 = static_cast<uint32_t>(zd0d);
+        const uint32_t b_hi = static_cast<uint32_t>(xd0d >> 32);
         auto pw1 = [&](int xblock) {   // xblock >= 0: first pw1 of bottleneck block `xblock`
             TR_MARK(1, 1);
             tr_wait_empty(&bars[TB_D1_EMPTY], d1_n);
@@ -328,8 +338,8 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                         const int kb = 2 * b2 + j;  // ring slot = K block of X
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            umma_f16(tm_d1, a0 + (kb * 1024 + 2 * k), xd0 + (kb * 1024 + k * 128), idesc,
-                                     (kb | k) ? 1u : 0u);
+                            umma_f16_lh(tm_d1, a0 + (kb * 1024 + 2 * k), a_hi, xd0 + (kb * 1024 + k * 128), b_hi,
+                                        idesc, (kb | k) ? 1u : 0u);
                     }
                     umma_commit(&bars[TB_PAIR_EMPTY + b2]);
                     if (b2 == TR_PAIRS - 1) umma_commit(&bars[TB_D1_FULL]);
@@ -340,8 +350,22 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             ++d1_n;
             TR_MARK(1, 3);
         };
+        uint32_t eca_n = 0;
         for (int b = 0; b < p.n_blocks; ++b) {
             const int nch = p.blk[b].n_chunks;
+            if (b > 0 && p.blk[b].eca_chunk0 >= 0) {
+                // the compute warps consume the Wc tiles; hand the ring slots back on their behalf
+                for (int m = 0; m < 3; ++m) {
+#pragma unroll
+                    for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
+                        tr_wait_full(&bars[TB_ECA_DONE + b2], eca_n);
+                        if (leader) mbar_arrive(&bars[TB_PAIR_EMPTY + b2]);
+                        __syncwarp();
+                    }
+                    par ^= 1;
+                    ++eca_n;
+                }
+            }
             pw1(b);
             for (int c = 0; c < nch; ++c) {
                 if (c + 1 < nch) pw1(-1);
@@ -361,8 +385,8 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                         for (int kh = 0; kh < 2; ++kh) {
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
-                                umma_f16(tm_d2 + m * 128, a0 + ((2 * m + kh) * 1024 + 2 * k),
-                                         zd0 + (kh * 1024 + k * 128), idesc, (kh | k) ? 1u : acc0);
+                                umma_f16_lh(tm_d2 + m * 128, a0 + ((2 * m + kh) * 1024 + 2 * k), a_hi,
+                                            zd0 + (kh * 1024 + k * 128), b_hi, idesc, (kh | k) ? 1u : acc0);
                         }
                         umma_commit(&bars[TB_PAIR_EMPTY + m]);
                         if (last_chunk) umma_commit(&bars[TB_D2_FULL + m]);  // output block m complete
@@ -414,11 +438,66 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             mbar_arrive(&bars[TB_X_READY + 2]);
         }
 
-        uint32_t d1_n = 0, z_n = 0;
+        uint32_t d1_n = 0, z_n = 0, gcount = 0;   // gcount = ring groups (laps) so far
         int trace_n = 0;
         unsigned long long* const ctrace = warp == 2 ? tr_trace : nullptr;
+        float* const zmean = reinterpret_cast<float*>(smem + TR_Z_OFF);  // [2 pos][384] while Z is idle
         for (int b = 0; b < p.n_blocks; ++b) {
             const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks, ks = p.blk[b].ksize;
+            if (b > 0 && p.blk[b].eca_chunk0 >= 0) {
+                // ---- ECA on the block input (builder_util.py:49-80, 481-483), inside the kernel:
+                // gate[o] = hardsigmoid(Wc[o,:] . mean + b[o]) on CUDA cores, Wc tiles [128 rows x
+                // 64 K] arriving through the weight ring; x' = x * gate in place, block m at a time.
+                const float* eb = p.bias2 + p.blk[b].eca_bias_off;
+                const float* mrow = zmean + h * 384;
+#pragma unroll 1
+                for (int m = 0; m < 3; ++m) {
+                    const float ebias = __ldg(eb + m * 128 + r);
+                    float acc = 0.0f;
+#pragma unroll 1
+                    for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
+                        mbar_wait(&bars[TB_PAIR_FULL + b2], gcount & 1);
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) {
+                            const int kb = 2 * b2 + j;
+                            const uint8_t* wrow = smem + TR_RING_OFF + kb * TR_SLOT_BYTES + r * 128;
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) {
+                                const uint4 wv = *reinterpret_cast<const uint4*>(wrow + ((c ^ key) << 4));
+                                const float4 m0 = *reinterpret_cast<const float4*>(mrow + kb * 64 + c * 8);
+                                const float4 m1 = *reinterpret_cast<const float4*>(mrow + kb * 64 + c * 8 + 4);
+                                const float2 w0 = unpack_act2(wv.x), w1 = unpack_act2(wv.y),
+                                             w2 = unpack_act2(wv.z), w3 = unpack_act2(wv.w);
+                                acc = fmaf(w0.x, m0.x, acc); acc = fmaf(w0.y, m0.y, acc);
+                                acc = fmaf(w1.x, m0.z, acc); acc = fmaf(w1.y, m0.w, acc);
+                                acc = fmaf(w2.x, m1.x, acc); acc = fmaf(w2.y, m1.y, acc);
+                                acc = fmaf(w3.x, m1.z, acc); acc = fmaf(w3.y, m1.w, acc);
+                            }
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&bars[TB_ECA_DONE + b2]);
+                    }
+                    ++gcount;
+                    // torch.nn.Hardsigmoid: relu6(x + 3) / 6
+                    const float g = fminf(fmaxf((acc + ebias) * (1.0f / 6.0f) + 0.5f, 0.0f), 1.0f);
+                    uint8_t* xrow = smem + TR_X_OFF + m * 32768 + row_off;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        uint4* px = reinterpret_cast<uint4*>(xrow + ((j ^ key) << 4));
+                        uint4 v = *px;
+                        float2 a = unpack_act2(v.x), bb = unpack_act2(v.y), c = unpack_act2(v.z), d = unpack_act2(v.w);
+                        v.x = pack_act2(a.x * g, a.y * g);
+                        v.y = pack_act2(bb.x * g, bb.y * g);
+                        v.z = pack_act2(c.x * g, c.y * g);
+                        v.w = pack_act2(d.x * g, d.y * g);
+                        *px = v;
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&bars[TB_X_READY + m]);
+                }
+            }
+            gcount += 2 * nch;
             {
                 const float* par0 = p.par + static_cast<size_t>(g0) * TR_PAR_FLOATS;
                 uint8_t* zrow = smem + TR_Z_OFF + row_off;
@@ -430,8 +509,10 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             // ---- block epilogue: x <- x + D2 + b2, in place in shared memory ----
             const bool last = (b + 1 == p.n_blocks);
             const float* b2 = p.bias2 + p.blk[b].bias2_off;
-            const bool want_sums = last && p.sums != nullptr;
-#pragma unroll 1
+            const bool want_means = !last && p.blk[b + 1].eca_chunk0 >= 0;  // next block gates its input
+            const bool want_sums = (last && p.sums != nullptr) || want_means;
+            float sums3[3];
+#pragma unroll
             for (int m = 0; m < 3; ++m) {
                 const float bias = __ldg(b2 + m * 128 + r);
                 { unsigned long long* tr_trace = ctrace; TR_MARK(2, 7); }
@@ -464,12 +545,19 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                     }
                     *px = make_uint4(ou[0], ou[1], ou[2], ou[3]);
                 }
-                if (want_sums) p.sums[static_cast<size_t>(pos) * 384 + m * 128 + r] = s;
+                sums3[m] = s;
+                if (last && p.sums != nullptr) p.sums[static_cast<size_t>(pos) * 384 + m * 128 + r] = s;
                 tc_fence_before();
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (!last && lane == 0) mbar_arrive(&bars[TB_X_READY + m]);
+                if (!last && !want_means && lane == 0) mbar_arrive(&bars[TB_X_READY + m]);
                 { unsigned long long* tr_trace = ctrace; TR_MARK(2, 9); }
+            }
+            if (want_means) {
+                // every pw2 of this block has completed (D2_FULL[2]), so Z is idle: park the means there
+#pragma unroll
+                for (int m = 0; m < 3; ++m) zmean[h * 384 + m * 128 + r] = sums3[m] * (1.0f / 64.0f);
+                named_bar_sync(2, TR_COMPUTE);
             }
         }
         // ---- run output: shared-memory tile -> global (TMA store) ----
