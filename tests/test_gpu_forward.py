@@ -159,3 +159,29 @@ def test_load_errors_return_false(tmp_path):
     assert not e.enqueueInferenceHalf(np.zeros((8, 74, 8, 8), np.float16), 0)   # nothing loaded
     assert not e.synchronizeInferenceHalf(HalfInferenceOutputs(), 0)
     e.close()
+
+
+def test_cpp_engine_shim_bench_tool(tmp_path, blob):
+    """The C++ Engine (include/hm_engine.hpp) driving the reference's `bench` loop
+    (benchmark.cc:15-57) through the C ABI: loadNetwork from a file, runInferenceHalf, and the
+    enqueue/synchronize overlap pattern of searchthread.cc:661-708."""
+    import os
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.join(root, "hivemind_b200")
+    exe = tmp_path / "hm_bench"
+    cmd = ["g++", "-O1", "-std=c++17", "-I" + os.path.join(root, "include"), os.path.join(root, "tools", "hm_bench.cc"),
+           "-L" + lib_dir, "-lhm_engine", "-Wl,-rpath," + lib_dir, "-o", str(exe)]
+    if os.path.isdir("/usr/local/cuda/include"):
+        cmd.insert(4, "-I/usr/local/cuda/include")
+    assert subprocess.run(cmd, capture_output=True, text=True).returncode == 0
+    w = tmp_path / "net.hvmw"
+    w.write_bytes(blob)
+    r = subprocess.run([str(exe), str(w), "20", "64", "--overlap"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    rates = [float(ln.split(":")[1]) for ln in r.stdout.splitlines() if ln.startswith("Positions per second")]
+    assert len(rates) == 2 and all(x > 0 for x in rates), r.stdout
+    # a missing weight file is reported the reference's way: message on stderr, non-zero exit
+    r = subprocess.run([str(exe), str(tmp_path / "missing.hvmw"), "1", "8"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 1 and "[ERROR]" in r.stderr
