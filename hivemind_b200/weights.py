@@ -196,3 +196,46 @@ def random_hvmw(seed: int = 0, path=None) -> bytes:
     """Seeded random-init RISEv3.3 weights as an .hvmw blob (what bench.py loads)."""
     spec = risev33_spec()
     return write_hvmw(path, fold_state_dict(random_state_dict(spec, seed), spec), spec["arch"])
+
+
+def convert_checkpoint(src: str, dst: str) -> Dict[str, np.ndarray]:
+    """Reference training checkpoint -> .hvmw.  `src` is a file written by the reference's
+    ``save_torch_state`` (src/training/trainer_agent.py:871-890: a dict with
+    ``model_state_dict``) or a bare ``state_dict``; a ``module.`` / ``_orig_mod.`` prefix left by
+    DataParallel / torch.compile wrappers is dropped.  Fails on missing or mis-shaped tensors."""
+    import torch
+
+    ckpt = torch.load(src, map_location="cpu", weights_only=True)
+    sd = ckpt.get("model_state_dict", ckpt) if isinstance(ckpt, dict) else ckpt
+    clean: Dict[str, np.ndarray] = {}
+    for k, v in sd.items():
+        for prefix in ("module.", "_orig_mod."):
+            if k.startswith(prefix):
+                k = k[len(prefix):]
+        clean[k] = v.detach().to(torch.float32).cpu().numpy()
+    spec = risev33_spec()
+    want = random_state_dict(spec, seed=0)
+    missing = sorted(set(want) - set(clean))
+    if missing:
+        raise KeyError(f"checkpoint lacks {len(missing)} tensors of risev33, e.g. {missing[:3]}")
+    bad = [k for k in want if tuple(clean[k].shape) != tuple(want[k].shape)]
+    if bad:
+        raise ValueError(f"shape mismatch for {bad[:3]}")
+    folded = fold_state_dict(clean, spec)
+    write_hvmw(dst, folded, spec["arch"])
+    return folded
+
+
+if __name__ == "__main__":
+    import sys
+
+    if len(sys.argv) == 3:
+        convert_checkpoint(sys.argv[1], sys.argv[2])
+        print(f"wrote {sys.argv[2]}")
+    elif len(sys.argv) == 4 and sys.argv[1] == "--random":
+        random_hvmw(int(sys.argv[2]), sys.argv[3])
+        print(f"wrote {sys.argv[3]}")
+    else:
+        print("usage: python -m hivemind_b200.weights <checkpoint.tar|state_dict.pt> <out.hvmw>\n"
+              "       python -m hivemind_b200.weights --random <seed> <out.hvmw>")
+        sys.exit(2)

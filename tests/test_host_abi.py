@@ -165,3 +165,23 @@ def test_two_rank_gloo_sharded_evaluation(tmp_path):
     assert r.returncode == 0, r.stderr[-2000:]
     line = [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT")]
     assert line and line[0].split()[1] == "True" and line[0].split()[3] == "True", r.stdout
+
+
+def test_checkpoint_conversion_cli(tmp_path):
+    """Reference-format checkpoint ({'model_state_dict': ...}, trainer_agent.py:871-890) -> .hvmw
+    equals folding the same tensors directly; a truncated checkpoint is refused."""
+    import torch
+
+    from hivemind_b200 import weights as W
+
+    sd = W.random_state_dict(seed=11)
+    ck = tmp_path / "model.tar"
+    torch.save({"model_state_dict": {"module." + k: torch.from_numpy(v) for k, v in sd.items()}}, ck)
+    out = tmp_path / "net.hvmw"
+    r = subprocess.run([sys.executable, "-m", "hivemind_b200.weights", str(ck), str(out)], capture_output=True, text=True, cwd=ROOT)
+    assert r.returncode == 0, r.stderr
+    assert out.read_bytes() == W.write_hvmw(None, W.fold_state_dict(sd))
+    sd.pop(next(iter(sd)))
+    torch.save({k: torch.from_numpy(v) for k, v in sd.items()}, ck)
+    with pytest.raises(KeyError):
+        W.convert_checkpoint(str(ck), str(out))
