@@ -1,0 +1,62 @@
+"""Pins oracle/forward_oracle.py (the CPU fp32 restatement of RISEv3.3 on folded tensors):
+(a) against the committed golden outputs that oracle/make_golden.py produced from the reference
+    PyTorch model itself (tests/golden/forward_risev33.npz) — runs everywhere;
+(b) against the reference model imported from /root/reference, where that exists."""
+import os
+
+import numpy as np
+import pytest
+
+N = 24  # positions: the torch fp32 CPU forward of these takes a few seconds
+
+
+@pytest.fixture(scope="module")
+def folded_and_sd():
+    from hivemind_b200 import weights as W
+
+    sd = W.random_state_dict(seed=0)
+    return W.fold_state_dict(sd), sd
+
+
+@pytest.fixture(scope="module")
+def oracle_out(oracle, gold_positions, folded_and_sd):
+    from oracle.forward_oracle import ForwardOracle
+
+    planes = oracle.encode_planes(gold_positions["packed"][:N], "f32")
+    return planes, ForwardOracle(folded_and_sd[0]).forward(planes)
+
+
+def test_forward_oracle_matches_reference_golden_outputs(oracle_out, gold_forward, gold_positions):
+    _, out = oracle_out
+    assert int(gold_forward["weight_seed"]) == 0 and int(gold_forward["param_count"]) == 14_122_085
+    np.testing.assert_allclose(out["value"], gold_forward["value"][:N], atol=2e-5)
+    np.testing.assert_allclose(out["wdl"], gold_forward["wdl"][:N], atol=2e-4, rtol=1e-4)
+    np.testing.assert_allclose(out["moves_left"], gold_forward["moves_left"][:N], atol=2e-5)
+    np.testing.assert_allclose(out["pi_a"][:8], gold_forward["pi_a_first8"], atol=5e-4, rtol=1e-4)
+    np.testing.assert_allclose(out["pi_b"][:8], gold_forward["pi_b_first8"], atol=5e-4, rtol=1e-4)
+
+
+def test_forward_oracle_priors_match_reference_golden(oracle, oracle_out, gold_forward, gold_positions):
+    """Legal-move priors from the oracle's logits vs those the reference model + reference softmax gave."""
+    from conftest import kl_divergence
+
+    _, out = oracle_out
+    offs, moves, packed = gold_positions["offsets"], gold_positions["moves"], gold_positions["packed"]
+    worst = 0.0
+    for g in range(N):
+        for bn in range(2):
+            lo, hi = offs[2 * g + bn], offs[2 * g + bn + 1]
+            stm = int(packed[g]["board"][bn]["flags"] & 1)
+            p = oracle.priors_f32(out["pi_a" if bn == 0 else "pi_b"][g], moves[lo:hi], stm)
+            worst = max(worst, kl_divergence(gold_forward["priors_f32"][lo:hi], p))
+    assert worst < 1e-6, worst
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/src/architectures"), reason="reference tree not present")
+def test_forward_oracle_matches_imported_reference_model(oracle_out, folded_and_sd):
+    from oracle.forward_oracle import reference_forward, reference_model
+
+    planes, out = oracle_out
+    ref = reference_forward(reference_model(folded_and_sd[1]), planes[:8])
+    for k in ("value", "wdl", "moves_left", "pi_a", "pi_b"):
+        np.testing.assert_allclose(out[k][:8], ref[k], atol=5e-4, rtol=1e-4, err_msg=k)
