@@ -51,6 +51,20 @@ def risev33_spec() -> dict:
     }
 
 
+def crossboard_spec() -> dict:
+    """``crossboard-risev33`` (rise_mobile_v3.py:852-888, class CrossBoardRiseV3 :281-412): the
+    same stem + 15 blocks, then board tokens, 2 cross-board attention layers, value fusion and
+    per-board 192-channel policy heads."""
+    spec = risev33_spec()
+    spec.update({"arch": ARCH_CROSSBOARD_RISEV33, "attention_dim": 192, "attention_heads": 6,
+                 "attention_layers": 2, "board_channels": 37, "mlp_ratio": 2})
+    return spec
+
+
+def spec_for_arch(arch: int) -> dict:
+    return crossboard_spec() if arch == ARCH_CROSSBOARD_RISEV33 else risev33_spec()
+
+
 def _bn(rng, c, prefix, sd, gamma_lo=0.5, gamma_hi=1.5):
     sd[prefix + ".weight"] = rng.uniform(gamma_lo, gamma_hi, c).astype(np.float32)
     sd[prefix + ".bias"] = (0.1 * rng.standard_normal(c)).astype(np.float32)
@@ -97,12 +111,52 @@ def random_state_dict(spec: dict | None = None, seed: int = 0) -> Dict[str, np.n
     sd["value_head.body_final.0.bias"] = (0.1 * rng.standard_normal(fc)).astype(np.float32)
     sd["value_head.body_final.2.weight"] = (rng.standard_normal((1, fc)) / np.sqrt(fc)).astype(np.float32)
     sd["value_head.body_final.2.bias"] = (0.1 * rng.standard_normal(1)).astype(np.float32)
+    pc = spec["policy_channels"]
+    if spec["arch"] == ARCH_CROSSBOARD_RISEV33:
+        _random_crossboard(rng, spec, sd)
+        return sd
     sd["policy_heads.shared_body.0.weight"] = _conv(rng, (C, C, 3, 3))
     _bn(rng, C, "policy_heads.shared_body.1", sd)
-    pc = spec["policy_channels"]
     for b in range(2):
         sd[f"policy_heads.board_projections.{b}.weight"] = _conv(rng, (pc, C, 3, 3), gain=1.2)
     return sd
+
+
+def _random_crossboard(rng, spec, sd):
+    """Parameters of CrossBoardRiseV3 beyond the trunk and value head, under the reference's
+    state_dict names (rise_mobile_v3.py:299-351)."""
+    C, D, pc, bc = spec["channels"], spec["attention_dim"], spec["policy_channels"], spec["board_channels"]
+    f32 = np.float32
+    for b in range(2):
+        sd[f"policy_heads.{b}.body.0.weight"] = _conv(rng, (D, D, 3, 3))
+        _bn(rng, D, f"policy_heads.{b}.body.1", sd)
+        sd[f"policy_heads.{b}.body.3.weight"] = _conv(rng, (pc, D, 3, 3), gain=1.2)
+    for b in range(2):
+        sd[f"board_token_projections.{b}.0.weight"] = _conv(rng, (D, C + bc, 1, 1))
+        _bn(rng, D, f"board_token_projections.{b}.1", sd)
+    sd["position_embedding"] = (0.3 * rng.standard_normal((1, 64, D))).astype(f32)
+    sd["board_embedding"] = (0.3 * rng.standard_normal((2, 1, D))).astype(f32)
+    sd["pocket_projection.weight"] = (rng.standard_normal((D, 5)) * 2.0).astype(f32)
+    sd["pocket_projection.bias"] = (0.2 * rng.standard_normal(D)).astype(f32)
+    sd["scalar_projection.weight"] = (rng.standard_normal((D, 1))).astype(f32)
+    sd["scalar_projection.bias"] = (0.2 * rng.standard_normal(D)).astype(f32)
+    sd["context_role_embedding"] = (0.3 * rng.standard_normal((1, 7, D))).astype(f32)
+    H = D * spec["mlp_ratio"]
+    for l in range(spec["attention_layers"]):
+        p = f"cross_board_blocks.{l}."
+        for n in ("query_norm", "memory_norm", "mlp_norm"):
+            sd[p + n + ".weight"] = rng.uniform(0.7, 1.3, D).astype(f32)
+            sd[p + n + ".bias"] = (0.1 * rng.standard_normal(D)).astype(f32)
+        sd[p + "cross_attention.in_proj_weight"] = (rng.standard_normal((3 * D, D)) * (1.5 / np.sqrt(D))).astype(f32)
+        sd[p + "cross_attention.in_proj_bias"] = (0.1 * rng.standard_normal(3 * D)).astype(f32)
+        sd[p + "cross_attention.out_proj.weight"] = (rng.standard_normal((D, D)) / np.sqrt(D)).astype(f32)
+        sd[p + "cross_attention.out_proj.bias"] = (0.1 * rng.standard_normal(D)).astype(f32)
+        sd[p + "mlp.0.weight"] = (rng.standard_normal((H, D)) * np.sqrt(2.0 / D)).astype(f32)
+        sd[p + "mlp.0.bias"] = (0.1 * rng.standard_normal(H)).astype(f32)
+        sd[p + "mlp.2.weight"] = (rng.standard_normal((D, H)) / np.sqrt(H)).astype(f32)
+        sd[p + "mlp.2.bias"] = (0.1 * rng.standard_normal(D)).astype(f32)
+    sd["value_fusion.0.weight"] = _conv(rng, (C, 2 * D, 1, 1))
+    _bn(rng, C, "value_fusion.1", sd)
 
 
 def _fold(w: np.ndarray, sd, bn_prefix: str):
@@ -141,12 +195,51 @@ def fold_state_dict(sd: Dict[str, np.ndarray], spec: dict | None = None) -> Dict
     out["value.wdl.b"] = sd["value_head.body_wdl.0.bias"].astype(np.float32)
     out["value.plys.w"] = sd["value_head.body_plys.0.weight"].astype(np.float32)
     out["value.plys.b"] = sd["value_head.body_plys.0.bias"].astype(np.float32)
+    if spec["arch"] == ARCH_CROSSBOARD_RISEV33:
+        _fold_crossboard(sd, spec, out)
+        return out
     out["policy.shared.w"], out["policy.shared.b"] = _fold(
         sd["policy_heads.shared_body.0.weight"], sd, "policy_heads.shared_body.1"
     )
     out["policy.a.w"] = sd["policy_heads.board_projections.0.weight"].astype(np.float32)
     out["policy.b.w"] = sd["policy_heads.board_projections.1.weight"].astype(np.float32)
     return out
+
+
+def _fold_crossboard(sd, spec, out):
+    C, D = spec["channels"], spec["attention_dim"]
+    f32 = np.float32
+    for b in range(2):
+        w, bias = _fold(sd[f"board_token_projections.{b}.0.weight"], sd, f"board_token_projections.{b}.1")
+        w = w.reshape(D, -1)
+        out[f"tok{b}.wt"] = np.ascontiguousarray(w[:, :C])   # trunk channels
+        out[f"tok{b}.wp"] = np.ascontiguousarray(w[:, C:])   # that board's 37 input planes
+        out[f"tok{b}.b"] = bias
+        w, bias = _fold(sd[f"policy_heads.{b}.body.0.weight"], sd, f"policy_heads.{b}.body.1")
+        out[f"pol{b}.c1.w"], out[f"pol{b}.c1.b"] = w, bias
+        out[f"pol{b}.c2.w"] = sd[f"policy_heads.{b}.body.3.weight"].astype(f32)
+    out["pos_emb"] = sd["position_embedding"].reshape(64, D).astype(f32)
+    out["board_emb"] = sd["board_embedding"].reshape(2, D).astype(f32)
+    out["ctx_role"] = sd["context_role_embedding"].reshape(7, D).astype(f32)
+    out["pocket.w"] = sd["pocket_projection.weight"].astype(f32)
+    out["pocket.b"] = sd["pocket_projection.bias"].astype(f32)
+    out["scalar.w"] = sd["scalar_projection.weight"].astype(f32)
+    out["scalar.b"] = sd["scalar_projection.bias"].astype(f32)
+    for l in range(spec["attention_layers"]):
+        p, q = f"cross_board_blocks.{l}.", f"xl{l}."
+        for src, dst in (("query_norm", "qn"), ("memory_norm", "mn"), ("mlp_norm", "ln")):
+            out[q + dst + ".w"] = sd[p + src + ".weight"].astype(f32)
+            out[q + dst + ".b"] = sd[p + src + ".bias"].astype(f32)
+        out[q + "in.w"] = sd[p + "cross_attention.in_proj_weight"].astype(f32)
+        out[q + "in.b"] = sd[p + "cross_attention.in_proj_bias"].astype(f32)
+        out[q + "out.w"] = sd[p + "cross_attention.out_proj.weight"].astype(f32)
+        out[q + "out.b"] = sd[p + "cross_attention.out_proj.bias"].astype(f32)
+        out[q + "fc1.w"] = sd[p + "mlp.0.weight"].astype(f32)
+        out[q + "fc1.b"] = sd[p + "mlp.0.bias"].astype(f32)
+        out[q + "fc2.w"] = sd[p + "mlp.2.weight"].astype(f32)
+        out[q + "fc2.b"] = sd[p + "mlp.2.bias"].astype(f32)
+    w, bias = _fold(sd["value_fusion.0.weight"], sd, "value_fusion.1")
+    out["vfuse.w"], out["vfuse.b"] = w.reshape(C, 2 * D), bias
 
 
 def write_hvmw(path_or_none, tensors: Dict[str, np.ndarray], arch: int = ARCH_RISEV33) -> bytes:
@@ -192,9 +285,9 @@ def read_hvmw(raw_or_path) -> Dict[str, np.ndarray]:
     return out
 
 
-def random_hvmw(seed: int = 0, path=None) -> bytes:
-    """Seeded random-init RISEv3.3 weights as an .hvmw blob (what bench.py loads)."""
-    spec = risev33_spec()
+def random_hvmw(seed: int = 0, path=None, arch: int = ARCH_RISEV33) -> bytes:
+    """Seeded random-init weights as an .hvmw blob (what bench.py loads)."""
+    spec = spec_for_arch(arch)
     return write_hvmw(path, fold_state_dict(random_state_dict(spec, seed), spec), spec["arch"])
 
 

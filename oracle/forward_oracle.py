@@ -64,6 +64,11 @@ class ForwardOracle:
             y = F.conv2d(y, t[q + "pw2.w"][:, :, None, None], t[q + "pw2.b"])
             x = x + y  # builder_util.py:483, no activation after the add
             inter[f"block{i}"] = x
+        cross = "tok0.wt" in t
+        if cross:
+            maps = self._crossboard(_t(planes), x, inter)
+            x = F.relu(F.conv2d(torch.cat(maps, dim=1), t["vfuse.w"][:, :, None, None], t["vfuse.b"]))
+            inter["value_fusion"] = x
         # value head (builder_util.py:311-324)
         v = F.relu(F.conv2d(x, t["value.conv.w"][:, :, None, None], t["value.conv.b"]))
         inter["value_feat"] = v
@@ -72,11 +77,20 @@ class ForwardOracle:
         plys = torch.sigmoid(F.linear(flat, t["value.plys.w"], t["value.plys.b"]))
         sm = torch.softmax(wdl, dim=1)
         value = sm[:, 2] - sm[:, 0]
-        # shared policy heads (rise_mobile_v3.py:52-57)
-        s = F.relu(F.conv2d(x, t["policy.shared.w"], t["policy.shared.b"], padding=1))
-        inter["policy_shared"] = s
-        pi_a = F.conv2d(s, t["policy.a.w"], None, padding=1).reshape(x.shape[0], -1)
-        pi_b = F.conv2d(s, t["policy.b.w"], None, padding=1).reshape(x.shape[0], -1)
+        if cross:
+            # per-board _PolicyHead(192) on that board's map (rise_mobile_v3.py:336-347, builder_util.py:206-243)
+            pis = []
+            for b in range(2):
+                s = F.relu(F.conv2d(maps[b], t[f"pol{b}.c1.w"], t[f"pol{b}.c1.b"], padding=1))
+                inter[f"policy_c1_{b}"] = s
+                pis.append(F.conv2d(s, t[f"pol{b}.c2.w"], None, padding=1).reshape(x.shape[0], -1))
+            pi_a, pi_b = pis
+        else:
+            # shared policy heads (rise_mobile_v3.py:52-57)
+            s = F.relu(F.conv2d(x, t["policy.shared.w"], t["policy.shared.b"], padding=1))
+            inter["policy_shared"] = s
+            pi_a = F.conv2d(s, t["policy.a.w"], None, padding=1).reshape(x.shape[0], -1)
+            pi_b = F.conv2d(s, t["policy.b.w"], None, padding=1).reshape(x.shape[0], -1)
         out = {
             "value": value.numpy(),
             "wdl": wdl.numpy(),
@@ -87,6 +101,50 @@ class ForwardOracle:
         if return_intermediates:
             out["inter"] = {k: v.numpy() for k, v in inter.items()}
         return out
+
+
+    def _crossboard(self, planes, trunk, inter):
+        """CrossBoardRiseV3.forward between the trunk and the heads (rise_mobile_v3.py:371-401),
+        written out with explicit matrix products instead of nn.MultiheadAttention."""
+        t = self.t
+        B, D, heads = planes.shape[0], t["pos_emb"].shape[1], 6
+        dh = D // heads
+        toks = []
+        for b in range(2):  # :374-385 — 1x1 conv over cat(trunk, that board's 37 planes) + BN + ReLU
+            w = torch.cat((t[f"tok{b}.wt"], t[f"tok{b}.wp"]), dim=1)[:, :, None, None]
+            m = F.relu(F.conv2d(torch.cat((trunk, planes[:, 37 * b: 37 * b + 37]), dim=1), w, t[f"tok{b}.b"]))
+            toks.append(m.flatten(2).transpose(1, 2) + t["pos_emb"][None] + t["board_emb"][b][None, None])
+        inter["tokens0"] = torch.stack(toks, 1)
+        # :353-369 — 4 pocket tokens + 3 scalar tokens from spatial means of input planes
+        mean = planes.mean(dim=(2, 3))
+        ctx = [F.linear(mean[:, lo:lo + 5], t["pocket.w"], t["pocket.b"]) for lo in (12, 17, 49, 54)]
+        ctx += [F.linear(mean[:, c:c + 1], t["scalar.w"], t["scalar.b"]) for c in (25, 62, 31)]
+        ctx = torch.stack(ctx, dim=1) + t["ctx_role"][None]
+        inter["context"] = ctx
+        n_layers = 0
+        while f"xl{n_layers}.in.w" in t:
+            n_layers += 1
+        for l in range(n_layers):
+            q_ = f"xl{l}."
+            wq, wk, wv = t[q_ + "in.w"].split(D, dim=0)
+            bq, bk, bv = t[q_ + "in.b"].split(D, dim=0)
+
+            def update(board, other):  # :262-271
+                mem = torch.cat((other, ctx), dim=1)
+                qn = F.layer_norm(board, (D,), t[q_ + "qn.w"], t[q_ + "qn.b"])
+                mn = F.layer_norm(mem, (D,), t[q_ + "mn.w"], t[q_ + "mn.b"])
+                Q = F.linear(qn, wq, bq).view(B, -1, heads, dh).transpose(1, 2)
+                K = F.linear(mn, wk, bk).view(B, -1, heads, dh).transpose(1, 2)
+                V = F.linear(mn, wv, bv).view(B, -1, heads, dh).transpose(1, 2)
+                P = torch.softmax(Q @ K.transpose(2, 3) / np.sqrt(dh), dim=-1)
+                att = (P @ V).transpose(1, 2).reshape(B, -1, D)
+                x1 = board + F.linear(att, t[q_ + "out.w"], t[q_ + "out.b"])
+                h = F.gelu(F.linear(F.layer_norm(x1, (D,), t[q_ + "ln.w"], t[q_ + "ln.b"]), t[q_ + "fc1.w"], t[q_ + "fc1.b"]))
+                return x1 + F.linear(h, t[q_ + "fc2.w"], t[q_ + "fc2.b"])
+
+            toks = [update(toks[0], toks[1]), update(toks[1], toks[0])]  # both from pre-update tokens (:273-278)
+            inter[f"tokens{l + 1}"] = torch.stack(toks, 1)
+        return [tk.transpose(1, 2).reshape(B, D, 8, 8) for tk in toks]
 
 
 def reference_model(state_dict: Dict[str, np.ndarray]):
@@ -102,7 +160,7 @@ def reference_model(state_dict: Dict[str, np.ndarray]):
     for p in (ref, stub):
         if p not in sys.path:
             sys.path.insert(0, p)
-    from src.architectures.rise_mobile_v3 import get_rise_v33_model  # noqa: E402
+    from src.architectures.rise_mobile_v3 import get_cross_board_rise_v33_model, get_rise_v33_model  # noqa: E402
 
     class Args:  # src/training/train_loop.py:95-116 with use_wdl = use_plys_to_end = True
         input_shape = (74, 8, 8)
@@ -114,7 +172,10 @@ def reference_model(state_dict: Dict[str, np.ndarray]):
         use_mlp_wdl_ply = False
         shared_policy_trunk = True
 
-    model = get_rise_v33_model(Args()).eval()
+    if "cross_board_blocks.0.query_norm.weight" in state_dict:
+        model = get_cross_board_rise_v33_model(Args()).eval()  # forces shared_policy_trunk=False itself (:286-290)
+    else:
+        model = get_rise_v33_model(Args()).eval()
     model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in state_dict.items()}, strict=True)
     return model
 

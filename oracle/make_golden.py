@@ -113,27 +113,27 @@ def main():
             kat[name + f".uci{bn}"] = np.array([b.move_uci(bn, m) for m in acts])
     np.savez_compressed(os.path.join(GOLD, "reference_kat.npz"), **kat)
 
-    # ---- stage F: reference PyTorch forward on seeded weights ----------------------------------
-    spec = W.risev33_spec()
-    sd = W.random_state_dict(spec, WEIGHT_SEED)
-    model = reference_model(sd)
-    out = reference_forward(model, planes_f32)
-    legal_logits = np.zeros(moves.size, np.float32)
-    ref_priors = np.zeros(moves.size, np.float32)
-    for g, b in enumerate(boards):
-        for bn in range(2):
-            lo, hi = offsets[2 * g + bn], offsets[2 * g + bn + 1]
-            pol = out["pi_a" if bn == 0 else "pi_b"][g]
-            idx = indices[lo:hi]
-            legal_logits[lo:hi] = np.where(idx >= 0, pol[np.maximum(idx, 0)], -np.inf)
-            ref_priors[lo:hi] = b.priors_f32(bn, pol, moves[lo:hi])
-    np.savez_compressed(
-        os.path.join(GOLD, "forward_risev33.npz"),
-        weight_seed=np.array(WEIGHT_SEED), value=out["value"], wdl=out["wdl"], moves_left=out["moves_left"],
-        legal_logits=legal_logits, priors_f32=ref_priors,
-        pi_a_first8=out["pi_a"][:8], pi_b_first8=out["pi_b"][:8],
-        param_count=np.array(sum(p.numel() for p in model.parameters())),
-    )
+    # ---- stages F and X: reference PyTorch forward on seeded weights -------------------------
+    for spec, fname in ((W.risev33_spec(), "forward_risev33.npz"), (W.crossboard_spec(), "forward_crossboard.npz")):
+        sd = W.random_state_dict(spec, WEIGHT_SEED)
+        model = reference_model(sd)
+        out = reference_forward(model, planes_f32)
+        legal_logits = np.zeros(moves.size, np.float32)
+        ref_priors = np.zeros(moves.size, np.float32)
+        for g, b in enumerate(boards):
+            for bn in range(2):
+                lo, hi = offsets[2 * g + bn], offsets[2 * g + bn + 1]
+                pol = out["pi_a" if bn == 0 else "pi_b"][g]
+                idx = indices[lo:hi]
+                legal_logits[lo:hi] = np.where(idx >= 0, pol[np.maximum(idx, 0)], -np.inf)
+                ref_priors[lo:hi] = b.priors_f32(bn, pol, moves[lo:hi])
+        np.savez_compressed(
+            os.path.join(GOLD, fname),
+            weight_seed=np.array(WEIGHT_SEED), value=out["value"], wdl=out["wdl"], moves_left=out["moves_left"],
+            legal_logits=legal_logits, priors_f32=ref_priors,
+            pi_a_first8=out["pi_a"][:8], pi_b_first8=out["pi_b"][:8],
+            param_count=np.array(sum(p.numel() for p in model.parameters())),
+        )
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 

@@ -10,12 +10,25 @@ import pytest
 N = 24  # positions: the torch fp32 CPU forward of these takes a few seconds
 
 
+@pytest.fixture(scope="module", params=["risev33", "crossboard"])
+def arch(request):
+    return request.param
+
+
 @pytest.fixture(scope="module")
-def folded_and_sd():
+def gold_forward(arch):  # overrides the session fixture: per architecture
+    from conftest import GOLD
+
+    return dict(np.load(os.path.join(GOLD, f"forward_{arch}.npz")))
+
+
+@pytest.fixture(scope="module")
+def folded_and_sd(arch):
     from hivemind_b200 import weights as W
 
-    sd = W.random_state_dict(seed=0)
-    return W.fold_state_dict(sd), sd
+    spec = W.crossboard_spec() if arch == "crossboard" else W.risev33_spec()
+    sd = W.random_state_dict(spec, seed=0)
+    return W.fold_state_dict(sd, spec), sd
 
 
 @pytest.fixture(scope="module")
@@ -28,7 +41,8 @@ def oracle_out(oracle, gold_positions, folded_and_sd):
 
 def test_forward_oracle_matches_reference_golden_outputs(oracle_out, gold_forward, gold_positions):
     _, out = oracle_out
-    assert int(gold_forward["weight_seed"]) == 0 and int(gold_forward["param_count"]) == 14_122_085
+    assert int(gold_forward["weight_seed"]) == 0
+    assert int(gold_forward["param_count"]) in (14_122_085, 14_127_269)  # risev33, crossboard
     np.testing.assert_allclose(out["value"], gold_forward["value"][:N], atol=2e-5)
     np.testing.assert_allclose(out["wdl"], gold_forward["wdl"][:N], atol=2e-4, rtol=1e-4)
     np.testing.assert_allclose(out["moves_left"], gold_forward["moves_left"][:N], atol=2e-5)
