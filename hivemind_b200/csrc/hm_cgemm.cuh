@@ -37,8 +37,10 @@ struct CgemmParams {
     const float* bias;  // [cout] or nullptr
     void* out;          // [pos][out_channels][64], act_t or fp32
     int out_channels;   // channel count of the output tensor
-    int relu;
+    int relu;           // activation: 0 none, 1 ReLU, 2 GELU (erf form, nn.GELU default)
     int out_f32;
+    const act_t* residual;  // optional [pos][out_channels][64], added before the activation
+    int stages;         // ring depth (1..CG_STAGES); shallow-K 1x1 layers use 1 so that 3 CTAs share an SM
 };
 
 constexpr int CG_THREADS = 192;
@@ -48,6 +50,7 @@ constexpr int CG_STAGES = 3;
 // and issuer loops (a 4-MMA stage cannot hide it: tools/probes/probe_mmaring.cu).
 constexpr int CG_STAGE_BYTES = 65536;
 constexpr int CG_SMEM = CG_STAGES * CG_STAGE_BYTES + 256 + 1024;
+constexpr int cg_smem_bytes(int stages) { return stages * CG_STAGE_BYTES + 256 + 1024; }
 
 __global__ void __launch_bounds__(CG_THREADS)
 cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
@@ -55,7 +58,8 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
     extern __shared__ uint8_t cg_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cg_smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + CG_STAGES * CG_STAGE_BYTES);
+    const int n_stages = p.stages;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + n_stages * CG_STAGE_BYTES);
     uint64_t* empty_bar = full_bar + CG_STAGES;
     uint64_t* accum_bar = empty_bar + CG_STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
@@ -68,7 +72,7 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmW);
         tma_prefetch_desc(&tmX);
-        for (int s = 0; s < CG_STAGES; ++s) {
+        for (int s = 0; s < n_stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
@@ -106,7 +110,7 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
                         tma_load_3d(dst + 49152, &tmX, &full_bar[stage], sq0, kp * 128 + 64, pos0);
                     }
                     __syncwarp();
-                    if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
+                    if (++stage == n_stages) { stage = 0; phase ^= 1; }
                 }
             }
         }
@@ -136,7 +140,7 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
                         umma_commit(&empty_bar[stage]);
                     }
                     __syncwarp();
-                    if (++stage == CG_STAGES) { stage = 0; phase ^= 1; }
+                    if (++stage == n_stages) { stage = 0; phase ^= 1; }
                 }
             }
         }
@@ -175,9 +179,26 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
             if (!valid) continue;
             const int pos = tile * 2 + (c0 >> 6);
             const size_t row = (static_cast<size_t>(pos) * p.out_channels + ch) * 64 + (c0 & 63);
-            if (p.relu) {
+            if (p.residual != nullptr) {
+                const uint4* rr = reinterpret_cast<const uint4*>(p.residual + row);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint4 u = __ldg(rr + j);
+                    const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        const float2 f = unpack_act2(w4[t]);
+                        v[8 * j + 2 * t] += f.x;
+                        v[8 * j + 2 * t + 1] += f.y;
+                    }
+                }
+            }
+            if (p.relu == 1) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+            } else if (p.relu == 2) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = 0.5f * v[j] * (1.0f + erff(v[j] * 0.70710678118654752f));
             }
             if (p.out_f32) {
                 float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + row);

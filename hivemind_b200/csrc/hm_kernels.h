@@ -30,6 +30,21 @@ void launch_value_tail(const act_t* feat, const float* w4, const float* b4, int 
                        float* raw5, __half* value_h, __half* wdl_h, __half* ml_h,
                        cudaStream_t s);
 
+// ---- stage X (crossboard-risev33, rise_mobile_v3.py:242-412), hm_xboard.cu ------------------------
+// tokens: fp16 [n][2 boards][192][64] channel-major; see the kernels for the formulas
+void launch_token_embed(const float* pre, const act_t* planes, const float* wp, const float* bias,
+                        const float* pos_emb, const float* board_emb, act_t* tok, int n, cudaStream_t s);
+void launch_context_tokens(const act_t* planes, const float* pocket_w, const float* pocket_b,
+                           const float* scalar_w, const float* scalar_b, const float* role, float* ctx,
+                           int n, cudaStream_t s);
+void launch_token_layernorm(const act_t* x, const float* g1, const float* b1, act_t* y1, const float* g2,
+                            const float* b2, act_t* y2, int n2, cudaStream_t s);
+void launch_context_kv(const float* ctx, const float* g, const float* b, const float* wkv_t,
+                       const float* bkv, float* ckv, int n, cudaStream_t s);
+void launch_cross_attention(const act_t* q, const act_t* kv, const float* ckv, act_t* att, int n,
+                            cudaStream_t s);
+bool xboard_prepare();
+
 // ---- stage D ------------------------------------------------------------------------
 // get_normalized_probability for both boards of n_pos positions (utils.h:226-243) reading
 // the fp32 logits [n][146][64] (index (pos*2+board)*4672 + ch*64+sq).

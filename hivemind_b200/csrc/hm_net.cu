@@ -102,9 +102,9 @@ static bool make_tm_weights(CUtensorMap* tm, const void* w, size_t rows, int kco
 // channels x 2 positions = one MN-major B-operand block (also the trunk's tile load / store).
 // A box shifted by +-8 squares reads zeros off the board, one shifted beyond the last channel
 // reads zeros too (convolution padding and K padding for free).
-static bool make_tm_act3(CUtensorMap* tm, const void* x, int n, int C) {
+static bool make_tm_act3(CUtensorMap* tm, const void* x, int n, int C, int pos_stride_ch = 0) {
     cuuint64_t dims[3] = {64, static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(n)};
-    cuuint64_t strides[2] = {128, static_cast<cuuint64_t>(C) * 128};
+    cuuint64_t strides[2] = {128, static_cast<cuuint64_t>(pos_stride_ch ? pos_stride_ch : C) * 128};
     cuuint32_t box[3] = {64, 64, 2};
     cuuint32_t es[3] = {1, 1, 1};
     CUresult r = g_encode(tm, HM_TMA_DTYPE, 3, const_cast<void*>(x), dims, strides,
@@ -149,29 +149,125 @@ static bool finish_dense(Net& net, DenseLayer& L, const std::vector<act_t>& w,
     }
     return make_tm_weights(&L.tm_w, L.w, L.n_rows, L.ksize * L.ksize * L.cpad);
 }
-static bool make_dense(Net& net, DenseLayer& L, const std::string& name, const HvmwTensor* w,
-                       const HvmwTensor* b) {
-    if (!w || w->dims.size() < 2) { set_error("missing tensor " + name + ".w"); return false; }
+// w: fp32 [cout][cin][k][k]; K per tap is padded to a multiple of 128 (cgemm stages hold two
+// 64-channel blocks).
+static bool make_dense_raw(Net& net, DenseLayer& L, const std::string& name, const float* w, int cout,
+                           int cin, int ksize, const float* b) {
     L.name = name;
-    L.cout = w->dims[0];
-    L.cin = w->dims[1];
-    L.ksize = w->dims.size() == 4 ? w->dims[2] : 1;
-    L.cpad = round_up(L.cin, 64);
+    L.cout = cout;
+    L.cin = cin;
+    L.ksize = ksize;
+    L.cpad = round_up(L.cin, 128);
     L.n_rows = round_up(L.cout, 128);
     const int ktot = L.ksize * L.ksize * L.cpad;
     std::vector<act_t> packed(static_cast<size_t>(L.n_rows) * ktot, float_to_act(0.0f));
-    pack_conv(packed, ktot, L.cpad, w->data, L.cout, L.cin, L.ksize, 0);
+    pack_conv(packed, ktot, L.cpad, w, L.cout, L.cin, L.ksize, 0);
     std::vector<float> bias;
-    if (b) bias.assign(b->data, b->data + b->numel());
-    net.param_count += w->numel() + (b ? b->numel() : 0);
+    if (b) bias.assign(b, b + cout);
+    net.param_count += static_cast<size_t>(cout) * cin * ksize * ksize + (b ? cout : 0);
     return finish_dense(net, L, packed, b ? &bias : nullptr);
+}
+static bool make_dense(Net& net, DenseLayer& L, const std::string& name, const HvmwTensor* w,
+                       const HvmwTensor* b) {
+    if (!w || w->dims.size() < 2) { set_error("missing tensor " + name + ".w"); return false; }
+    if (b && b->numel() != w->dims[0]) { set_error("bias size mismatch for " + name); return false; }
+    return make_dense_raw(net, L, name, w->data, w->dims[0], w->dims[1], w->dims.size() == 4 ? w->dims[2] : 1,
+                          b ? b->data : nullptr);
+}
+static float* upload_tensor(Net& net, const HvmwTensor* t, size_t expect, const std::string& name) {
+    if (!t || t->numel() != expect) { set_error("missing / mis-sized tensor " + name); return nullptr; }
+    net.param_count += expect;
+    return upload(net, std::vector<float>(t->data, t->data + expect));
+}
+
+// Everything of CrossBoardRiseV3 between the trunk and the value head (rise_mobile_v3.py:299-351).
+static bool build_crossboard(Net& net, const HvmwBlob& blob) {
+    auto T = [&](const std::string& n) { return blob.find(n); };
+    constexpr int D = 192, C = 384, BC = 37;
+    const HvmwTensor *t0 = T("tok0.wt"), *t1 = T("tok1.wt");
+    if (!t0 || !t1 || t0->numel() != static_cast<size_t>(D) * C || t1->numel() != static_cast<size_t>(D) * C) {
+        set_error("missing token projection tensors");
+        return false;
+    }
+    std::vector<float> stacked(static_cast<size_t>(2) * D * C);
+    std::copy(t0->data, t0->data + D * C, stacked.begin());
+    std::copy(t1->data, t1->data + D * C, stacked.begin() + D * C);
+    if (!make_dense_raw(net, net.tok_proj, "tokens.proj", stacked.data(), 2 * D, C, 1, nullptr)) return false;
+    {
+        const HvmwTensor *p0 = T("tok0.wp"), *p1 = T("tok1.wp"), *b0 = T("tok0.b"), *b1 = T("tok1.b");
+        if (!p0 || !p1 || !b0 || !b1 || p0->numel() != static_cast<size_t>(D) * BC || b0->numel() != D) {
+            set_error("missing token projection plane weights");
+            return false;
+        }
+        std::vector<float> wp(2 * D * BC), bb(2 * D);
+        std::copy(p0->data, p0->data + D * BC, wp.begin());
+        std::copy(p1->data, p1->data + D * BC, wp.begin() + D * BC);
+        std::copy(b0->data, b0->data + D, bb.begin());
+        std::copy(b1->data, b1->data + D, bb.begin() + D);
+        net.tok_wp = upload(net, wp);
+        net.tok_bias = upload(net, bb);
+        net.param_count += wp.size() + bb.size();
+        if (!net.tok_wp || !net.tok_bias) return false;
+    }
+    {   // position embedding [64 squares][192] -> channel-major [192][64]
+        const HvmwTensor* pe = T("pos_emb");
+        if (!pe || pe->numel() != static_cast<size_t>(64) * D) { set_error("missing pos_emb"); return false; }
+        std::vector<float> t(64 * D);
+        for (int sq = 0; sq < 64; ++sq)
+            for (int o = 0; o < D; ++o) t[o * 64 + sq] = pe->data[sq * D + o];
+        net.pos_emb = upload(net, t);
+        net.param_count += t.size();
+        if (!net.pos_emb) return false;
+    }
+    if (!(net.board_emb = upload_tensor(net, T("board_emb"), 2 * D, "board_emb"))) return false;
+    if (!(net.ctx_role = upload_tensor(net, T("ctx_role"), 7 * D, "ctx_role"))) return false;
+    if (!(net.pocket_w = upload_tensor(net, T("pocket.w"), D * 5, "pocket.w"))) return false;
+    if (!(net.pocket_b = upload_tensor(net, T("pocket.b"), D, "pocket.b"))) return false;
+    if (!(net.scalar_w = upload_tensor(net, T("scalar.w"), D, "scalar.w"))) return false;
+    if (!(net.scalar_b = upload_tensor(net, T("scalar.b"), D, "scalar.b"))) return false;
+    for (int l = 0;; ++l) {
+        const std::string q = "xl" + std::to_string(l) + ".";
+        const HvmwTensor *inw = T(q + "in.w"), *inb = T(q + "in.b");
+        if (!inw) break;
+        if (!inb || inw->numel() != static_cast<size_t>(3) * D * D || inb->numel() != 3 * D) {
+            set_error("malformed attention in_proj of layer " + q);
+            return false;
+        }
+        net.xlayers.emplace_back();
+        XLayer& L = net.xlayers.back();
+        // nn.MultiheadAttention packs q | k | v rows in in_proj_weight
+        if (!make_dense_raw(net, L.wq, q + "q", inw->data, D, D, 1, inb->data)) return false;
+        if (!make_dense_raw(net, L.wkv, q + "kv", inw->data + D * D, 2 * D, D, 1, inb->data + D)) return false;
+        std::vector<float> wt(static_cast<size_t>(D) * 2 * D);
+        for (int o = 0; o < 2 * D; ++o)
+            for (int i = 0; i < D; ++i) wt[static_cast<size_t>(i) * 2 * D + o] = inw->data[static_cast<size_t>(D + o) * D + i];
+        L.wkv_t = upload(net, wt);
+        L.bkv = upload(net, std::vector<float>(inb->data + D, inb->data + 3 * D));
+        if (!L.wkv_t || !L.bkv) return false;
+        if (!make_dense(net, L.wo, q + "out", T(q + "out.w"), T(q + "out.b"))) return false;
+        if (!make_dense(net, L.fc1, q + "fc1", T(q + "fc1.w"), T(q + "fc1.b"))) return false;
+        if (!make_dense(net, L.fc2, q + "fc2", T(q + "fc2.w"), T(q + "fc2.b"))) return false;
+        if (!(L.qn_g = upload_tensor(net, T(q + "qn.w"), D, q + "qn.w")) || !(L.qn_b = upload_tensor(net, T(q + "qn.b"), D, q + "qn.b")) ||
+            !(L.mn_g = upload_tensor(net, T(q + "mn.w"), D, q + "mn.w")) || !(L.mn_b = upload_tensor(net, T(q + "mn.b"), D, q + "mn.b")) ||
+            !(L.ln_g = upload_tensor(net, T(q + "ln.w"), D, q + "ln.w")) || !(L.ln_b = upload_tensor(net, T(q + "ln.b"), D, q + "ln.b")))
+            return false;
+    }
+    if (net.xlayers.empty()) { set_error("crossboard network without attention layers"); return false; }
+    if (!make_dense(net, net.vfuse, "value.fusion", T("vfuse.w"), T("vfuse.b"))) return false;
+    for (int b = 0; b < 2; ++b) {
+        const std::string q = "pol" + std::to_string(b) + ".";
+        if (!make_dense(net, net.pol_c1[b], "policy" + std::to_string(b) + ".conv1", T(q + "c1.w"), T(q + "c1.b"))) return false;
+        if (!make_dense(net, net.pol_c2[b], "policy" + std::to_string(b) + ".conv2", T(q + "c2.w"), nullptr)) return false;
+        if (net.pol_c1[b].cin != D || net.pol_c2[b].cout != 73) { set_error("unexpected policy head shape"); return false; }
+    }
+    return true;
 }
 
 std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
     if (!tensormap_init()) return nullptr;
     auto net = std::make_unique<Net>();
     net->arch = blob.arch;
-    if (blob.arch != HM_ARCH_RISEV33) {
+    if (blob.arch != HM_ARCH_RISEV33 && blob.arch != HM_ARCH_CROSSBOARD_RISEV33) {
         set_error("architecture " + std::to_string(blob.arch) + " not supported by this build");
         return nullptr;
     }
@@ -280,6 +376,10 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
         net->value_b4 = upload(*net, b4);
         if (!net->value_w4 || !net->value_b4) return nullptr;
         net->param_count += ww->numel() + wb->numel() + pw->numel() + pb->numel();
+    }
+    if (net->arch == HM_ARCH_CROSSBOARD_RISEV33) {
+        if (!build_crossboard(*net, blob)) return nullptr;
+        return net;
     }
     // policy heads (shared trunk, two 73-channel projections stacked)
     if (!make_dense(*net, net->policy_shared, "policy.shared", T("policy.shared.w"), T("policy.shared.b"))) return nullptr;
@@ -396,32 +496,139 @@ static bool add_trunk_run(Worker& w, std::vector<Op>& ops, const Net& net, int f
     return true;
 }
 
-// One convolution as an Op: in = NCHW [n][cin_buf][64] -> out [n][out_channels][64].
-static bool add_dense(std::vector<Op>& ops, const DenseLayer& L, const act_t* in, int cin_buf,
-                      int n_pos, void* out, bool relu, bool out_f32, const char* suffix = "") {
+// One convolution as an Op: in = NCHW [in_n][in_C][64] (positions `in_stride_ch` channels apart,
+// 0 = dense) -> out [in_n][out_channels][64] (0 = L.cout), optional residual (same layout as out)
+// and activation (0 none, 1 ReLU, 2 GELU).
+struct DenseIO {
+    const act_t* in = nullptr;
+    int in_n = 0, in_C = 0, in_stride_ch = 0;
+    void* out = nullptr;
+    int out_channels = 0;
+    bool out_f32 = false;
+    int act = 0;
+    const act_t* residual = nullptr;
+    const char* suffix = "";
+};
+static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseIO& io) {
     CUtensorMap tm_x;
-    if (!make_tm_act3(&tm_x, in, n_pos, cin_buf)) return false;
+    if (!make_tm_act3(&tm_x, io.in, io.in_n, io.in_C, io.in_stride_ch)) return false;
     CgemmParams p{};
     p.m_blocks = L.n_rows / 128;
     p.n_valid = L.cout;
     p.ksize = L.ksize;
     p.kblocks = L.cpad / 64;
     p.bias = L.bias;
-    p.out = out;
-    p.out_channels = L.cout;
-    p.relu = relu ? 1 : 0;
-    p.out_f32 = out_f32 ? 1 : 0;
-    const int grid = (n_pos / 2) * p.m_blocks;
+    p.out = io.out;
+    p.out_channels = io.out_channels ? io.out_channels : L.cout;
+    p.relu = io.act;
+    p.out_f32 = io.out_f32 ? 1 : 0;
+    p.residual = io.residual;
+    // a 1x1 layer has only Cpad/128 <= 3 stage loads per CTA: a deep ring buys nothing, three
+    // co-resident CTAs (64 KB each, 128 TMEM columns) overlap one CTA's epilogue with another's MMAs
+    p.stages = L.ksize == 1 ? 1 : CG_STAGES;
+    const int smem = cg_smem_bytes(p.stages);
+    const int grid = (io.in_n / 2) * p.m_blocks;
     const CUtensorMap tm_w = L.tm_w;
     Op op;
-    op.name = L.name + suffix;
+    op.name = L.name + io.suffix;
     op.klass = "dense";
-    op.flops = 2.0 * L.macs_per_pos() * n_pos;
+    op.flops = 2.0 * L.macs_per_pos() * io.in_n;
     op.bytes = 0;
-    op.launch = [p, tm_w, tm_x, grid](cudaStream_t s) {
-        cgemm_kernel<<<grid, CG_THREADS, CG_SMEM, s>>>(p, tm_w, tm_x);
+    op.launch = [p, tm_w, tm_x, grid, smem](cudaStream_t s) {
+        cgemm_kernel<<<grid, CG_THREADS, smem, s>>>(p, tm_w, tm_x);
     };
     ops.push_back(std::move(op));
+    return true;
+}
+static bool add_dense(std::vector<Op>& ops, const DenseLayer& L, const act_t* in, int cin_buf,
+                      int n_pos, void* out, bool relu, bool out_f32, const char* suffix = "") {
+    DenseIO io;
+    io.in = in; io.in_n = n_pos; io.in_C = cin_buf; io.out = out; io.out_f32 = out_f32;
+    io.act = relu ? 1 : 0; io.suffix = suffix;
+    return add_dense_io(ops, L, io);
+}
+static void add_simple(std::vector<Op>& ops, const std::string& name, const char* klass, double bytes,
+                       std::function<void(cudaStream_t)> fn) {
+    Op op;
+    op.name = name;
+    op.klass = klass;
+    op.bytes = bytes;
+    op.launch = std::move(fn);
+    ops.push_back(std::move(op));
+}
+
+// crossboard-risev33 between the trunk and the heads (rise_mobile_v3.py:371-412): board tokens,
+// context tokens, the attention blocks, value fusion; leaves the final tokens in *tok_out and
+// the fused value input in w.d_fuse.
+static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int B, act_t** tok_out) {
+    const size_t nb = static_cast<size_t>(B);
+    bool ok = dev_alloc(w, &w.d_tokpre, nb * 384 * 64) && dev_alloc(w, &w.d_tok[0], nb * 384 * 64) &&
+              dev_alloc(w, &w.d_tok[1], nb * 384 * 64) && dev_alloc(w, &w.d_nq, nb * 384 * 64) &&
+              dev_alloc(w, &w.d_nm, nb * 384 * 64) && dev_alloc(w, &w.d_q, nb * 384 * 64) &&
+              dev_alloc(w, &w.d_kv, nb * 768 * 64) && dev_alloc(w, &w.d_att, nb * 384 * 64) &&
+              dev_alloc(w, &w.d_x1, nb * 384 * 64) && dev_alloc(w, &w.d_h, nb * 768 * 64) &&
+              dev_alloc(w, &w.d_fuse, nb * 384 * 64) && dev_alloc(w, &w.d_ctx, nb * 7 * 192) &&
+              dev_alloc(w, &w.d_ckv, nb * 7 * 384);
+    if (!ok || !xboard_prepare()) return false;
+    // X1/X2: trunk part of both token projections on the tensor cores, the 37 board planes,
+    // BN bias, ReLU and the embeddings in the follow-up kernel
+    {
+        DenseIO io;
+        io.in = w.d_trunk; io.in_n = B; io.in_C = 384; io.out = w.d_tokpre; io.out_f32 = true;
+        if (!add_dense_io(ops, net.tok_proj, io)) return false;
+        const float *pre = w.d_tokpre, *wp = net.tok_wp, *tb = net.tok_bias, *pe = net.pos_emb, *be = net.board_emb;
+        const act_t* planes = w.d_planes;
+        act_t* tok = w.d_tok[0];
+        add_simple(ops, "tokens.embed", "tokens", nb * 384 * 64 * 6.0,
+                   [=](cudaStream_t s) { launch_token_embed(pre, planes, wp, tb, pe, be, tok, B, s); });
+        const float *pw = net.pocket_w, *pb = net.pocket_b, *sw = net.scalar_w, *sb = net.scalar_b, *role = net.ctx_role;
+        float* ctx = w.d_ctx;
+        add_simple(ops, "tokens.context", "tokens", nb * 7 * 192 * 4.0,
+                   [=](cudaStream_t s) { launch_context_tokens(planes, pw, pb, sw, sb, role, ctx, B, s); });
+    }
+    w.debug_views["tokens0"] = {w.d_tok[0], {B, 384 * 64, 0}};
+    w.debug_views["context"] = {w.d_ctx, {B, 7 * 192, 1}};
+    int cur = 0;
+    for (size_t l = 0; l < net.xlayers.size(); ++l) {
+        const XLayer& L = net.xlayers[l];
+        const std::string q = "xl" + std::to_string(l) + ".";
+        act_t *tin = w.d_tok[cur], *tout = w.d_tok[cur ^ 1];
+        act_t *nq = w.d_nq, *nm = w.d_nm, *att = w.d_att, *x1 = w.d_x1, *qb = w.d_q, *kv = w.d_kv;
+        float *ctx = w.d_ctx, *ckv = w.d_ckv;
+        const float *qg = L.qn_g, *qbb = L.qn_b, *mg = L.mn_g, *mb = L.mn_b, *lg = L.ln_g, *lb = L.ln_b;
+        add_simple(ops, q + "norm_qm", "tokens", nb * 384 * 64 * 6.0,
+                   [=](cudaStream_t s) { launch_token_layernorm(tin, qg, qbb, nq, mg, mb, nm, 2 * B, s); });
+        DenseIO io;
+        io.in = nq; io.in_n = 2 * B; io.in_C = 192; io.out = qb;
+        if (!add_dense_io(ops, L.wq, io)) return false;
+        io.in = nm; io.out = kv;
+        if (!add_dense_io(ops, L.wkv, io)) return false;
+        const float *wkv_t = L.wkv_t, *bkv = L.bkv;
+        add_simple(ops, q + "context_kv", "tokens", nb * 7 * 384 * 4.0,
+                   [=](cudaStream_t s) { launch_context_kv(ctx, mg, mb, wkv_t, bkv, ckv, B, s); });
+        add_simple(ops, q + "attention", "attention", nb * 2 * (192.0 + 384 + 192) * 64 * 2,
+                   [=](cudaStream_t s) { launch_cross_attention(qb, kv, ckv, att, B, s); });
+        ops.back().flops = 2.0 * 2 * 64 * 71 * 192 * 2 * nb;  // QK^T and PV, both boards (CUDA cores)
+        io = DenseIO();
+        io.in = att; io.in_n = 2 * B; io.in_C = 192; io.out = x1; io.residual = tin;
+        if (!add_dense_io(ops, L.wo, io)) return false;
+        act_t* ln = w.d_nq;  // reuse
+        add_simple(ops, q + "norm_mlp", "tokens", nb * 384 * 64 * 4.0,
+                   [=](cudaStream_t s) { launch_token_layernorm(x1, lg, lb, ln, nullptr, nullptr, nullptr, 2 * B, s); });
+        io = DenseIO();
+        io.in = ln; io.in_n = 2 * B; io.in_C = 192; io.out = w.d_h; io.act = 2;
+        if (!add_dense_io(ops, L.fc1, io)) return false;
+        io = DenseIO();
+        io.in = w.d_h; io.in_n = 2 * B; io.in_C = 384; io.out = tout; io.residual = x1;
+        if (!add_dense_io(ops, L.fc2, io)) return false;
+        cur ^= 1;
+        w.debug_views["tokens" + std::to_string(l + 1)] = {tout, {B, 384 * 64, 0}};
+    }
+    *tok_out = w.d_tok[cur];
+    DenseIO io;
+    io.in = *tok_out; io.in_n = B; io.in_C = 384; io.out = w.d_fuse; io.act = 1;
+    if (!add_dense_io(ops, net.vfuse, io)) return false;
+    w.debug_views["value_fusion"] = {w.d_fuse, {B, 384 * 64, 0}};
     return true;
 }
 
@@ -493,7 +700,11 @@ static bool setup_worker(Engine* e, Worker& w) {
     }
     w.debug_views["planes"] = {w.d_planes, {B, HM_NB_INPUT_VALUES, 0}};
     w.debug_views["trunk"] = {w.d_trunk, {B, 384 * 64, 0}};
-    if (!add_dense(ops, net.value_conv, w.d_trunk, 384, B, w.d_vfeat, true, false)) return false;
+    const bool cross = net.arch == HM_ARCH_CROSSBOARD_RISEV33;
+    act_t* tokens = nullptr;
+    if (cross && !add_crossboard(w, ops, net, B, &tokens)) return false;
+    const act_t* value_in = cross ? w.d_fuse : w.d_trunk;
+    if (!add_dense(ops, net.value_conv, value_in, 384, B, w.d_vfeat, true, false)) return false;
     w.debug_views["value_feat"] = {w.d_vfeat, {B, 16 * 64, 0}};
     {
         Op op;
@@ -507,12 +718,33 @@ static bool setup_worker(Engine* e, Worker& w) {
         op.launch = [f, w4, b4, B, raw5, vh, wh, mh](cudaStream_t s) { launch_value_tail(f, w4, b4, B, raw5, vh, wh, mh, s); };
         ops.push_back(std::move(op));
     }
-    if (!add_dense(ops, net.policy_shared, w.d_trunk, 384, B, w.d_pol_shared, true, false)) return false;
     w.debug_views["policy_shared"] = {w.d_pol_shared, {B, 384 * 64, 0}};
     w.debug_views["logits"] = {w.d_logits, {B, POLICY_CH * 64, 1}};
-
-    // ---- reference-shaped post: dense fp16 policy maps, index ch*64+sq (rise_mobile_v3.py:55) ----
-    if (!add_dense(w.ops_dense_out, net.policy_proj, w.d_pol_shared, 384, B, w.d_pi, false, false, ".f16")) return false;
+    if (cross) {
+        // per-board _PolicyHead(192) on that board's token map (rise_mobile_v3.py:336-347): board b's
+        // map is channels [192b, 192b+192) of the token tensor; conv1 outputs go side by side into
+        // d_pol_shared, conv2 logits into rows [73b, 73b+73) of the stacked policy tensor
+        for (int b = 0; b < 2; ++b) {
+            DenseIO io;
+            io.in = tokens + static_cast<size_t>(b) * 192 * 64; io.in_n = B; io.in_C = 192; io.in_stride_ch = 384;
+            io.out = w.d_pol_shared + static_cast<size_t>(b) * 192 * 64; io.out_channels = 384; io.act = 1;
+            if (!add_dense_io(ops, net.pol_c1[b], io)) return false;
+        }
+        for (int b = 0; b < 2; ++b) {
+            DenseIO io;
+            io.in = w.d_pol_shared + static_cast<size_t>(b) * 192 * 64; io.in_n = B; io.in_C = 192; io.in_stride_ch = 384;
+            io.out_channels = POLICY_CH;
+            io.out = w.d_pi + static_cast<size_t>(b) * 73 * 64; io.suffix = ".f16";
+            if (!add_dense_io(w.ops_dense_out, net.pol_c2[b], io)) return false;
+            io.out = w.d_logits + static_cast<size_t>(b) * 73 * 64; io.out_f32 = true; io.suffix = "";
+            if (!add_dense_io(w.ops_fused_out, net.pol_c2[b], io)) return false;
+        }
+    } else {
+        if (!add_dense(ops, net.policy_shared, w.d_trunk, 384, B, w.d_pol_shared, true, false)) return false;
+        // reference-shaped post: dense fp16 policy maps, index ch*64+sq (rise_mobile_v3.py:55)
+        if (!add_dense(w.ops_dense_out, net.policy_proj, w.d_pol_shared, 384, B, w.d_pi, false, false, ".f16")) return false;
+        if (!add_dense(w.ops_fused_out, net.policy_proj, w.d_pol_shared, 384, B, w.d_logits, false, true)) return false;
+    }
     // ---- fused pre/post ---------------------------------------------------------------------
     {
         Op op;
@@ -529,7 +761,6 @@ static bool setup_worker(Engine* e, Worker& w) {
         op.launch = [pp, out, B, dt](cudaStream_t s) { launch_planes_nchw(pp, B, out, dt, s); };
         w.ops_fused_in.push_back(std::move(op));
     }
-    if (!add_dense(w.ops_fused_out, net.policy_proj, w.d_pol_shared, 384, B, w.d_logits, false, true)) return false;
     {
         Op op;
         op.name = "policy.priors";

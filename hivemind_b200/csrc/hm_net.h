@@ -59,6 +59,12 @@ struct Block {                 // one bottleneck block inside the trunk kernel (
     float* eca_b = nullptr;
     double macs_per_pos() const { return 2.0 * 64.0 * 384.0 * cop; }
 };
+struct XLayer {                // one _CrossBoardAttentionBlock (rise_mobile_v3.py:242-278)
+    DenseLayer wq, wkv, wo, fc1, fc2;   // 1x1 "convolutions" over channel-major tokens
+    float *qn_g = nullptr, *qn_b = nullptr, *mn_g = nullptr, *mn_b = nullptr, *ln_g = nullptr, *ln_b = nullptr;
+    float* wkv_t = nullptr;        // fp32 [192 in][384 out] for the 7 context tokens
+    float* bkv = nullptr;          // fp32 [384]
+};
 struct Net {
     int arch = HM_ARCH_RISEV33;
     int channels = 384;
@@ -76,6 +82,14 @@ struct Net {
     float* value_b4 = nullptr;   // [4]
     DenseLayer policy_shared;    // 3x3 384 -> 384
     DenseLayer policy_proj;      // 3x3 384 -> 146 (A: 0..72, B: 73..145)
+    // crossboard-risev33 only (arch 1)
+    DenseLayer tok_proj;          // 1x1 384 -> 384: trunk part of both board token projections stacked
+    float *tok_wp = nullptr, *tok_bias = nullptr;      // [2][192][37], [2][192]
+    float *pos_emb = nullptr, *board_emb = nullptr, *ctx_role = nullptr;
+    float *pocket_w = nullptr, *pocket_b = nullptr, *scalar_w = nullptr, *scalar_b = nullptr;
+    std::vector<XLayer> xlayers;
+    DenseLayer vfuse;             // 1x1 384 -> 384 on cat(board maps)
+    DenseLayer pol_c1[2], pol_c2[2];   // per-board _PolicyHead(192): 3x3 192->192, 3x3 192->73
     std::vector<void*> allocations;
     size_t param_count = 0;
     ~Net();
@@ -116,6 +130,11 @@ struct Worker {
     float* d_sums = nullptr;        // [B][384] channel sums for the next ECA gate
     float* d_gate = nullptr;        // [B][384]
     __half *d_value_h = nullptr, *d_wdl_h = nullptr, *d_ml_h = nullptr;
+    // crossboard-risev33 (arch 1): tokens [B][2][192][64] channel-major and their intermediates
+    float* d_tokpre = nullptr;      // fp32 [B][384][64]
+    act_t *d_tok[2] = {nullptr, nullptr}, *d_nq = nullptr, *d_nm = nullptr, *d_q = nullptr, *d_kv = nullptr,
+          *d_att = nullptr, *d_x1 = nullptr, *d_h = nullptr, *d_fuse = nullptr;
+    float *d_ctx = nullptr, *d_ckv = nullptr;
     // pinned host mirrors (engine-owned outputs, engine.h:45-51)
     hm_packed_pos* h_pos = nullptr;
     uint32_t* h_moves = nullptr;

@@ -1,0 +1,283 @@
+// hm_xboard.cu — the non-GEMM kernels of `crossboard-risev33` (SURVEY.md §8a stage X;
+// reference src/architectures/rise_mobile_v3.py:242-412, class CrossBoardRiseV3).
+//
+// Tokens stay in the network's channel-major layout: the token matrix of a board is the
+// transpose of its map, so `tok[pos][board][192][64]` (fp16) is at once the [64 tokens][192]
+// residual stream of the attention blocks and — read as [pos][384][64] — the
+// cat(board_a_map, board_b_map) the value fusion conv wants (:397-404).  Every Linear of the
+// blocks is therefore a 1x1 convolution on cgemm_kernel (hm_cgemm.cuh); what is left here is
+// the bandwidth work around them: token embedding, context tokens, LayerNorms, and the
+// 64x71 attention core.
+#include <cuda_fp16.h>
+#include <math.h>
+
+#include "hm_kernels.h"
+
+namespace hm {
+
+constexpr int XD = 192;      // attention_dim
+constexpr int XH = 6;        // heads
+constexpr int XDH = 32;      // head dim
+constexpr int XCTX = 7;      // context tokens
+constexpr float LN_EPS = 1e-5f;
+
+// ---- X1/X2: board tokens ---------------------------------------------------------------
+// pre: fp32 [n][384][64] = W_trunk(board) * trunk for both boards stacked (cgemm, no bias).
+// tok[pos][b][o][sq] = relu(pre + bias[b][o] + sum_c wp[b][o][c] * planes[pos][37b + c][sq])
+//                      + pos_emb_t[o][sq] + board_emb[b][o]        (rise_mobile_v3.py:374-385;
+//                      pos_emb_t = the position embedding transposed to channel-major at load)
+// grid (n, 2), 256 threads = 4 channel groups x 64 squares.
+__global__ void __launch_bounds__(256)
+token_embed_kernel(const float* __restrict__ pre, const act_t* __restrict__ planes,
+                   const float* __restrict__ wp, const float* __restrict__ bias,
+                   const float* __restrict__ pos_emb, const float* __restrict__ board_emb,
+                   act_t* __restrict__ tok) {
+    __shared__ float s_wp[XD * 37];
+    const int pos = blockIdx.x, b = blockIdx.y;
+    for (int i = threadIdx.x; i < XD * 37; i += 256) s_wp[i] = wp[b * XD * 37 + i];
+    const int sq = threadIdx.x & 63, grp = threadIdx.x >> 6;
+    float pl[37];
+#pragma unroll
+    for (int c = 0; c < 37; ++c)
+        pl[c] = act_to_float(planes[(static_cast<size_t>(pos) * 74 + 37 * b + c) * 64 + sq]);
+    __syncthreads();
+    for (int o = grp * 48; o < grp * 48 + 48; ++o) {
+        float v = pre[(static_cast<size_t>(pos) * 384 + b * XD + o) * 64 + sq] + bias[b * XD + o];
+        const float* w = s_wp + o * 37;
+#pragma unroll
+        for (int c = 0; c < 37; ++c) v = fmaf(w[c], pl[c], v);
+        v = fmaxf(v, 0.0f) + pos_emb[o * 64 + sq] + board_emb[b * XD + o];
+        tok[(static_cast<size_t>(pos) * 384 + b * XD + o) * 64 + sq] = float_to_act(v);
+    }
+}
+
+// ---- X3: context tokens ------------------------------------------------------------------
+// 4 pocket tokens Linear(5->192) on the spatial means of planes 12-16, 17-21, 49-53, 54-58 and
+// 3 scalar tokens Linear(1->192) on the means of planes 25, 62, 31, plus the role embedding
+// (rise_mobile_v3.py:353-369).  ctx: fp32 [n][7][192].  grid n, 192 threads.
+__global__ void __launch_bounds__(XD)
+context_tokens_kernel(const act_t* __restrict__ planes, const float* __restrict__ pocket_w,
+                      const float* __restrict__ pocket_b, const float* __restrict__ scalar_w,
+                      const float* __restrict__ scalar_b, const float* __restrict__ role,
+                      float* __restrict__ ctx) {
+    __shared__ float s_mean[23];
+    const int pos = blockIdx.x;
+    if (threadIdx.x < 23) {
+        const int t = threadIdx.x;
+        const int plane = t < 5 ? 12 + t : t < 10 ? 17 + (t - 5) : t < 15 ? 49 + (t - 10) : t < 20 ? 54 + (t - 15)
+                        : t == 20 ? 25 : t == 21 ? 62 : 31;
+        const act_t* p = planes + (static_cast<size_t>(pos) * 74 + plane) * 64;
+        float s = 0.0f;
+        for (int i = 0; i < 64; ++i) s += act_to_float(p[i]);
+        s_mean[t] = s * (1.0f / 64.0f);
+    }
+    __syncthreads();
+    const int o = threadIdx.x;
+    float* out = ctx + static_cast<size_t>(pos) * XCTX * XD;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        float v = pocket_b[o];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) v = fmaf(pocket_w[o * 5 + j], s_mean[t * 5 + j], v);
+        out[t * XD + o] = v + role[t * XD + o];
+    }
+#pragma unroll
+    for (int t = 0; t < 3; ++t)
+        out[(4 + t) * XD + o] = fmaf(scalar_w[o], s_mean[20 + t], scalar_b[o]) + role[(4 + t) * XD + o];
+}
+
+// ---- LayerNorm over the 192 channels of each token ----------------------------------------
+// x: [n2][192][64] (n2 = positions x boards).  One statistic, up to two affine outputs
+// (query_norm and memory_norm read the same tokens, rise_mobile_v3.py:263-268).
+// grid n2, 256 threads = 4 channel groups x 64 squares; each thread holds 48 channels.
+__global__ void __launch_bounds__(256)
+token_layernorm_kernel(const act_t* __restrict__ x, const float* __restrict__ g1,
+                       const float* __restrict__ b1, act_t* __restrict__ y1,
+                       const float* __restrict__ g2, const float* __restrict__ b2,
+                       act_t* __restrict__ y2) {
+    __shared__ float s_sum[4][64], s_sq[4][64];
+    const size_t base = static_cast<size_t>(blockIdx.x) * XD * 64;
+    const int sq = threadIdx.x & 63, grp = threadIdx.x >> 6;
+    float v[48];
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 48; ++i) {
+        v[i] = act_to_float(x[base + static_cast<size_t>(grp * 48 + i) * 64 + sq]);
+        s += v[i];
+    }
+    s_sum[grp][sq] = s;
+    __syncthreads();
+    const float mean = (s_sum[0][sq] + s_sum[1][sq] + s_sum[2][sq] + s_sum[3][sq]) * (1.0f / XD);
+    float q = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 48; ++i) {
+        v[i] -= mean;
+        q = fmaf(v[i], v[i], q);
+    }
+    s_sq[grp][sq] = q;
+    __syncthreads();
+    const float rstd = rsqrtf((s_sq[0][sq] + s_sq[1][sq] + s_sq[2][sq] + s_sq[3][sq]) * (1.0f / XD) + LN_EPS);
+#pragma unroll
+    for (int i = 0; i < 48; ++i) {
+        const int c = grp * 48 + i;
+        const float n = v[i] * rstd;
+        y1[base + static_cast<size_t>(c) * 64 + sq] = float_to_act(fmaf(n, g1[c], b1[c]));
+        if (y2 != nullptr) y2[base + static_cast<size_t>(c) * 64 + sq] = float_to_act(fmaf(n, g2[c], b2[c]));
+    }
+}
+
+// ---- K/V of the 7 context tokens -----------------------------------------------------------
+// mem = memory_norm(ctx); K = Wk mem + bk, V = Wv mem + bv (nn.MultiheadAttention in_proj rows
+// 192..575).  wkv_t: fp32 [192 in][384 out] (K outputs 0..191, V outputs 192..383), bkv [384].
+// ckv: fp32 [n][7][384].  grid n, 384 threads.
+__global__ void __launch_bounds__(384)
+context_kv_kernel(const float* __restrict__ ctx, const float* __restrict__ g, const float* __restrict__ b,
+                  const float* __restrict__ wkv_t, const float* __restrict__ bkv, float* __restrict__ ckv) {
+    __shared__ float s_n[XCTX][XD];
+    __shared__ float s_stat[XCTX][2];
+    const int pos = blockIdx.x;
+    const float* c = ctx + static_cast<size_t>(pos) * XCTX * XD;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp < XCTX) {
+        float s = 0.0f;
+        for (int i = lane; i < XD; i += 32) s += c[warp * XD + i];
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float mean = s * (1.0f / XD);
+        float q = 0.0f;
+        for (int i = lane; i < XD; i += 32) { const float d = c[warp * XD + i] - mean; q = fmaf(d, d, q); }
+        for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+        if (lane == 0) { s_stat[warp][0] = mean; s_stat[warp][1] = rsqrtf(q * (1.0f / XD) + LN_EPS); }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < XCTX * XD; i += 384) {
+        const int t = i / XD, ch = i - t * XD;
+        s_n[t][ch] = fmaf((c[i] - s_stat[t][0]) * s_stat[t][1], g[ch], b[ch]);
+    }
+    __syncthreads();
+    const int o = threadIdx.x;
+    float acc[XCTX];
+#pragma unroll
+    for (int t = 0; t < XCTX; ++t) acc[t] = bkv[o];
+    for (int i = 0; i < XD; ++i) {
+        const float w = wkv_t[i * 384 + o];
+#pragma unroll
+        for (int t = 0; t < XCTX; ++t) acc[t] = fmaf(w, s_n[t][i], acc[t]);
+    }
+#pragma unroll
+    for (int t = 0; t < XCTX; ++t) ckv[(static_cast<size_t>(pos) * XCTX + t) * 384 + o] = acc[t];
+}
+
+// ---- X4: cross-board attention core --------------------------------------------------------
+// For board i of a position: queries = its 64 tokens, memory = the OTHER board's 64 tokens + the
+// 7 context tokens (rise_mobile_v3.py:262-271), 6 heads of 32 channels, softmax(QK^T/sqrt(32))V.
+// q:  fp16 [n2][192][64]  (Wq * query_norm(tokens) + bq, channel-major)
+// kv: fp16 [n2][384][64]  (rows 0..191 = K, 192..383 = V of memory_norm(tokens))
+// ckv: fp32 [n][7][384]   (context K | V)
+// att: fp16 [n2][192][64] (heads concatenated, before out_proj)
+// grid n2 = positions x boards, 384 threads: thread = (head, query square).
+constexpr int XATT_SMEM = (384 * 64 + XCTX * 384) * 4;
+
+__global__ void __launch_bounds__(384)
+cross_attention_kernel(const act_t* __restrict__ q, const act_t* __restrict__ kv,
+                       const float* __restrict__ ckv, act_t* __restrict__ att) {
+    extern __shared__ float xs[];
+    float* s_kv = xs;                 // [384][64]: K rows then V rows of the other board
+    float* s_c = xs + 384 * 64;       // [7][384]
+    const int n2 = blockIdx.x, pos = n2 >> 1, other = n2 ^ 1;
+    {
+        // coalesced fill: consecutive threads convert consecutive 16-byte pieces (8 values)
+        const uint4* src = reinterpret_cast<const uint4*>(kv + static_cast<size_t>(other) * 384 * 64);
+        float4* dst = reinterpret_cast<float4*>(s_kv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int i = threadIdx.x + 384 * j;
+            const uint4 u = __ldg(src + i);
+            const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), c = unpack_act2(u.z), d = unpack_act2(u.w);
+            dst[2 * i] = make_float4(a.x, a.y, b.x, b.y);
+            dst[2 * i + 1] = make_float4(c.x, c.y, d.x, d.y);
+        }
+        for (int i = threadIdx.x; i < XCTX * 384; i += 384) s_c[i] = ckv[static_cast<size_t>(pos) * XCTX * 384 + i];
+    }
+    const int h = threadIdx.x >> 6, sq = threadIdx.x & 63;
+    float qv[XDH];
+    const float scale = 0.17677669529663689f;  // 1/sqrt(32)
+#pragma unroll
+    for (int c = 0; c < XDH; ++c)
+        qv[c] = act_to_float(q[(static_cast<size_t>(n2) * XD + h * XDH + c) * 64 + sq]) * scale;
+    __syncthreads();
+
+    float s[64 + XCTX];
+#pragma unroll
+    for (int k = 0; k < 64 + XCTX; ++k) s[k] = 0.0f;
+    const float* kh = s_kv + h * XDH * 64;
+#pragma unroll 4
+    for (int c = 0; c < XDH; ++c) {
+        const float4* row = reinterpret_cast<const float4*>(kh + c * 64);
+#pragma unroll
+        for (int k4 = 0; k4 < 16; ++k4) {
+            const float4 kk = row[k4];
+            s[4 * k4 + 0] = fmaf(qv[c], kk.x, s[4 * k4 + 0]);
+            s[4 * k4 + 1] = fmaf(qv[c], kk.y, s[4 * k4 + 1]);
+            s[4 * k4 + 2] = fmaf(qv[c], kk.z, s[4 * k4 + 2]);
+            s[4 * k4 + 3] = fmaf(qv[c], kk.w, s[4 * k4 + 3]);
+        }
+#pragma unroll
+        for (int t = 0; t < XCTX; ++t) s[64 + t] = fmaf(qv[c], s_c[t * 384 + h * XDH + c], s[64 + t]);
+    }
+    float mx = s[0];
+#pragma unroll
+    for (int k = 1; k < 64 + XCTX; ++k) mx = fmaxf(mx, s[k]);
+    float sum = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 64 + XCTX; ++k) {
+        s[k] = __expf(s[k] - mx);
+        sum += s[k];
+    }
+    const float inv = 1.0f / sum;
+    const float* vh = s_kv + (XD + h * XDH) * 64;
+#pragma unroll 4
+    for (int c = 0; c < XDH; ++c) {
+        const float4* row = reinterpret_cast<const float4*>(vh + c * 64);
+        float a = 0.0f;
+#pragma unroll
+        for (int k4 = 0; k4 < 16; ++k4) {
+            const float4 vv = row[k4];
+            a = fmaf(s[4 * k4 + 0], vv.x, a);
+            a = fmaf(s[4 * k4 + 1], vv.y, a);
+            a = fmaf(s[4 * k4 + 2], vv.z, a);
+            a = fmaf(s[4 * k4 + 3], vv.w, a);
+        }
+#pragma unroll
+        for (int t = 0; t < XCTX; ++t) a = fmaf(s[64 + t], s_c[t * 384 + XD + h * XDH + c], a);
+        att[(static_cast<size_t>(n2) * XD + h * XDH + c) * 64 + sq] = float_to_act(a * inv);
+    }
+}
+
+// ---- launchers ---------------------------------------------------------------------------
+void launch_token_embed(const float* pre, const act_t* planes, const float* wp, const float* bias,
+                        const float* pos_emb, const float* board_emb, act_t* tok, int n, cudaStream_t s) {
+    if (n > 0) token_embed_kernel<<<dim3(n, 2), 256, 0, s>>>(pre, planes, wp, bias, pos_emb, board_emb, tok);
+}
+void launch_context_tokens(const act_t* planes, const float* pocket_w, const float* pocket_b,
+                           const float* scalar_w, const float* scalar_b, const float* role, float* ctx,
+                           int n, cudaStream_t s) {
+    if (n > 0) context_tokens_kernel<<<n, XD, 0, s>>>(planes, pocket_w, pocket_b, scalar_w, scalar_b, role, ctx);
+}
+void launch_token_layernorm(const act_t* x, const float* g1, const float* b1, act_t* y1, const float* g2,
+                            const float* b2, act_t* y2, int n2, cudaStream_t s) {
+    if (n2 > 0) token_layernorm_kernel<<<n2, 256, 0, s>>>(x, g1, b1, y1, g2, b2, y2);
+}
+void launch_context_kv(const float* ctx, const float* g, const float* b, const float* wkv_t,
+                       const float* bkv, float* ckv, int n, cudaStream_t s) {
+    if (n > 0) context_kv_kernel<<<n, 384, 0, s>>>(ctx, g, b, wkv_t, bkv, ckv);
+}
+bool xboard_prepare() {
+    return cudaFuncSetAttribute(cross_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                XATT_SMEM) == cudaSuccess;
+}
+void launch_cross_attention(const act_t* q, const act_t* kv, const float* ckv, act_t* att, int n,
+                            cudaStream_t s) {
+    if (n > 0) cross_attention_kernel<<<2 * n, 384, XATT_SMEM, s>>>(q, kv, ckv, att);
+}
+
+}  // namespace hm

@@ -68,17 +68,17 @@ public:
     // `engineFile` (the TensorRT plan cache) has no counterpart and is ignored.
     bool loadNetwork(const std::string& onnxFile, const std::string& engineFile = std::string()) {
         (void)engineFile;
-        return ok(m_handle != nullptr && hm_engine_load(m_handle, onnxFile.c_str()) == 0, "loadNetwork");
+        return ok(m_handle != nullptr && hm_engine_load(m_handle, onnxFile.c_str()) != 0, "loadNetwork");
     }
     bool loadNetworkFromMemory(const void* blob, size_t bytes) {
-        return ok(m_handle != nullptr && hm_engine_load_memory(m_handle, blob, bytes) == 0, "loadNetworkFromMemory");
+        return ok(m_handle != nullptr && hm_engine_load_memory(m_handle, blob, bytes) != 0, "loadNetworkFromMemory");
     }
 
     // engine.h:72-73
     bool runInference(float* obs, float* value, float* piA, float* piB, float* wdl,
                       float* movesLeft, size_t workerIndex = 0) {
         return ok(m_handle != nullptr &&
-                      hm_engine_run_float(m_handle, obs, value, piA, piB, wdl, movesLeft, workerIndex) == 0,
+                      hm_engine_run_float(m_handle, obs, value, piA, piB, wdl, movesLeft, workerIndex) != 0,
                   "runInference");
     }
 
@@ -90,13 +90,13 @@ public:
     // engine.h:80
     bool enqueueInferenceHalf(const __half* obs, size_t workerIndex = 0) {
         return ok(m_handle != nullptr &&
-                      hm_engine_enqueue_half(m_handle, reinterpret_cast<const uint16_t*>(obs), workerIndex) == 0,
+                      hm_engine_enqueue_half(m_handle, reinterpret_cast<const uint16_t*>(obs), workerIndex) != 0,
                   "enqueueInferenceHalf");
     }
     // engine.h:81-82
     bool synchronizeInferenceHalf(HalfInferenceOutputs& outputs, size_t workerIndex = 0) {
         const uint16_t *v = nullptr, *a = nullptr, *b = nullptr, *w = nullptr, *m = nullptr;
-        if (m_handle == nullptr || hm_engine_sync_half(m_handle, workerIndex, &v, &a, &b, &w, &m) != 0)
+        if (m_handle == nullptr || hm_engine_sync_half(m_handle, workerIndex, &v, &a, &b, &w, &m) == 0)
             return ok(false, "synchronizeInferenceHalf");
         outputs.value = reinterpret_cast<const __half*>(v);
         outputs.policyA = reinterpret_cast<const __half*>(a);
@@ -118,12 +118,12 @@ public:
     bool enqueuePositions(const hm_packed_pos* pos, size_t nPos, const uint32_t* moves,
                           const uint32_t* moveOffsets, size_t workerIndex = 0) {
         return ok(m_handle != nullptr &&
-                      hm_engine_enqueue_positions(m_handle, pos, nPos, moves, moveOffsets, workerIndex) == 0,
+                      hm_engine_enqueue_positions(m_handle, pos, nPos, moves, moveOffsets, workerIndex) != 0,
                   "enqueuePositions");
     }
     bool synchronizePriors(PriorOutputs& out, size_t workerIndex = 0) {
         return ok(m_handle != nullptr &&
-                      hm_engine_sync_priors(m_handle, workerIndex, &out.priors, &out.values, &out.raw) == 0,
+                      hm_engine_sync_priors(m_handle, workerIndex, &out.priors, &out.values, &out.raw) != 0,
                   "synchronizePriors");
     }
     void setValueConfig(const hm_value_config& cfg) {

@@ -185,3 +185,52 @@ def test_cpp_engine_shim_bench_tool(tmp_path, blob):
     # a missing weight file is reported the reference's way: message on stderr, non-zero exit
     r = subprocess.run([str(exe), str(tmp_path / "missing.hvmw"), "1", "8"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 1 and "[ERROR]" in r.stderr
+
+
+# ---- crossboard-risev33 (SURVEY.md §8a stage X) ------------------------------------------------
+
+@pytest.fixture(scope="module")
+def cross_engine():
+    from hivemind_b200 import weights as W
+    from hivemind_b200.engine import Engine
+
+    e = Engine(0, 256, 1)
+    assert e.loadNetworkFromMemory(W.random_hvmw(seed=0, arch=W.ARCH_CROSSBOARD_RISEV33))
+    yield e
+    e.close()
+
+
+@pytest.fixture(scope="module")
+def gold_cross():
+    import os
+
+    from conftest import GOLD
+
+    return dict(np.load(os.path.join(GOLD, "forward_crossboard.npz")))
+
+
+def test_crossboard_fused_path_matches_reference_model(cross_engine, gold_positions, gold_cross):
+    """CrossBoardRiseV3 (rise_mobile_v3.py:281-412) outputs of the reference PyTorch model on the
+    256 golden positions vs the CUDA path (tokens, 2 cross-attention layers, value fusion,
+    per-board policy heads)."""
+    g, f = gold_positions, gold_cross
+    res = cross_engine.evaluatePositions(g["packed"], g["moves"], g["offsets"])
+    assert res is not None
+    priors, values, raw = res
+    assert np.abs(raw[:, 0] - f["value"]).max() <= VALUE_TOL
+    assert np.abs(raw[:, 4] - f["moves_left"]).max() <= VALUE_TOL
+    assert np.abs(raw[:, 1:4] - f["wdl"]).max() <= 5e-2
+    assert _max_kl(priors, f["priors_f32"], g["offsets"]) <= KL_TOL
+
+
+def test_crossboard_reference_shaped_half_path(cross_engine, oracle, gold_positions, gold_cross):
+    from hivemind_b200.engine import HalfInferenceOutputs
+
+    g, f = gold_positions, gold_cross
+    obs = oracle.encode_planes(g["packed"], "f16")
+    out = HalfInferenceOutputs()
+    assert cross_engine.runInferenceHalf(obs, out)
+    assert np.abs(out.value.astype(np.float32) - f["value"]).max() <= VALUE_TOL
+    assert np.abs(out.policyA[:8].astype(np.float32) - f["pi_a_first8"]).max() <= 0.1
+    assert np.abs(out.policyB[:8].astype(np.float32) - f["pi_b_first8"]).max() <= 0.1
+    assert cross_engine._L.hm_engine_arch(cross_engine._h) == 1
