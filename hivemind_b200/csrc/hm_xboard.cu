@@ -32,20 +32,30 @@ token_embed_kernel(const float* __restrict__ pre, const act_t* __restrict__ plan
                    const float* __restrict__ wp, const float* __restrict__ bias,
                    const float* __restrict__ pos_emb, const float* __restrict__ board_emb,
                    act_t* __restrict__ tok) {
-    __shared__ float s_wp[XD * 37];
+    __shared__ __align__(16) float s_wp[XD * 40];   // rows padded 37 -> 40 for 16-byte broadcast reads
     const int pos = blockIdx.x, b = blockIdx.y;
-    for (int i = threadIdx.x; i < XD * 37; i += 256) s_wp[i] = wp[b * XD * 37 + i];
+    for (int i = threadIdx.x; i < XD * 40; i += 256) {
+        const int o = i / 40, c = i - o * 40;
+        s_wp[i] = c < 37 ? wp[(b * XD + o) * 37 + c] : 0.0f;
+    }
     const int sq = threadIdx.x & 63, grp = threadIdx.x >> 6;
-    float pl[37];
+    float pl[40];
 #pragma unroll
     for (int c = 0; c < 37; ++c)
         pl[c] = act_to_float(planes[(static_cast<size_t>(pos) * 74 + 37 * b + c) * 64 + sq]);
+    pl[37] = pl[38] = pl[39] = 0.0f;
     __syncthreads();
     for (int o = grp * 48; o < grp * 48 + 48; ++o) {
         float v = pre[(static_cast<size_t>(pos) * 384 + b * XD + o) * 64 + sq] + bias[b * XD + o];
-        const float* w = s_wp + o * 37;
+        const float4* w = reinterpret_cast<const float4*>(s_wp + o * 40);
 #pragma unroll
-        for (int c = 0; c < 37; ++c) v = fmaf(w[c], pl[c], v);
+        for (int c4 = 0; c4 < 10; ++c4) {
+            const float4 ww = w[c4];
+            v = fmaf(ww.x, pl[4 * c4], v);
+            v = fmaf(ww.y, pl[4 * c4 + 1], v);
+            v = fmaf(ww.z, pl[4 * c4 + 2], v);
+            v = fmaf(ww.w, pl[4 * c4 + 3], v);
+        }
         v = fmaxf(v, 0.0f) + pos_emb[o * 64 + sq] + board_emb[b * XD + o];
         tok[(static_cast<size_t>(pos) * 384 + b * XD + o) * 64 + sq] = float_to_act(v);
     }
@@ -130,41 +140,45 @@ token_layernorm_kernel(const act_t* __restrict__ x, const float* __restrict__ g1
 // mem = memory_norm(ctx); K = Wk mem + bk, V = Wv mem + bv (nn.MultiheadAttention in_proj rows
 // 192..575).  wkv_t: fp32 [192 in][384 out] (K outputs 0..191, V outputs 192..383), bkv [384].
 // ckv: fp32 [n][7][384].  grid n, 384 threads.
+constexpr int CKV_POS = 4;   // positions per CTA: the 295 KB weight matrix is read once for all of them
 __global__ void __launch_bounds__(384)
 context_kv_kernel(const float* __restrict__ ctx, const float* __restrict__ g, const float* __restrict__ b,
-                  const float* __restrict__ wkv_t, const float* __restrict__ bkv, float* __restrict__ ckv) {
-    __shared__ float s_n[XCTX][XD];
-    __shared__ float s_stat[XCTX][2];
-    const int pos = blockIdx.x;
-    const float* c = ctx + static_cast<size_t>(pos) * XCTX * XD;
+                  const float* __restrict__ wkv_t, const float* __restrict__ bkv, float* __restrict__ ckv, int n) {
+    constexpr int NT = CKV_POS * XCTX;   // 28 tokens
+    __shared__ float s_n[NT][XD];
+    __shared__ float s_stat[NT][2];
+    const int pos0 = blockIdx.x * CKV_POS;
+    const int n_tok = min(CKV_POS, n - pos0) * XCTX;
+    const float* c = ctx + static_cast<size_t>(pos0) * XCTX * XD;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp < XCTX) {
+    for (int t = warp; t < n_tok; t += 12) {
         float s = 0.0f;
-        for (int i = lane; i < XD; i += 32) s += c[warp * XD + i];
+        for (int i = lane; i < XD; i += 32) s += c[t * XD + i];
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
         const float mean = s * (1.0f / XD);
         float q = 0.0f;
-        for (int i = lane; i < XD; i += 32) { const float d = c[warp * XD + i] - mean; q = fmaf(d, d, q); }
+        for (int i = lane; i < XD; i += 32) { const float d = c[t * XD + i] - mean; q = fmaf(d, d, q); }
         for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
-        if (lane == 0) { s_stat[warp][0] = mean; s_stat[warp][1] = rsqrtf(q * (1.0f / XD) + LN_EPS); }
+        if (lane == 0) { s_stat[t][0] = mean; s_stat[t][1] = rsqrtf(q * (1.0f / XD) + LN_EPS); }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < XCTX * XD; i += 384) {
+    for (int i = threadIdx.x; i < NT * XD; i += 384) {
         const int t = i / XD, ch = i - t * XD;
-        s_n[t][ch] = fmaf((c[i] - s_stat[t][0]) * s_stat[t][1], g[ch], b[ch]);
+        s_n[t][ch] = t < n_tok ? fmaf((c[i] - s_stat[t][0]) * s_stat[t][1], g[ch], b[ch]) : 0.0f;
     }
     __syncthreads();
     const int o = threadIdx.x;
-    float acc[XCTX];
+    float acc[NT];
 #pragma unroll
-    for (int t = 0; t < XCTX; ++t) acc[t] = bkv[o];
+    for (int t = 0; t < NT; ++t) acc[t] = bkv[o];
     for (int i = 0; i < XD; ++i) {
         const float w = wkv_t[i * 384 + o];
 #pragma unroll
-        for (int t = 0; t < XCTX; ++t) acc[t] = fmaf(w, s_n[t][i], acc[t]);
+        for (int t = 0; t < NT; ++t) acc[t] = fmaf(w, s_n[t][i], acc[t]);
     }
 #pragma unroll
-    for (int t = 0; t < XCTX; ++t) ckv[(static_cast<size_t>(pos) * XCTX + t) * 384 + o] = acc[t];
+    for (int t = 0; t < NT; ++t)
+        if (t < n_tok) ckv[(static_cast<size_t>(pos0) * XCTX + t) * 384 + o] = acc[t];
 }
 
 // ---- X4: cross-board attention core --------------------------------------------------------
@@ -210,7 +224,7 @@ cross_attention_kernel(const act_t* __restrict__ q, const act_t* __restrict__ kv
 #pragma unroll
     for (int k = 0; k < 64 + XCTX; ++k) s[k] = 0.0f;
     const float* kh = s_kv + h * XDH * 64;
-#pragma unroll 4
+#pragma unroll
     for (int c = 0; c < XDH; ++c) {
         const float4* row = reinterpret_cast<const float4*>(kh + c * 64);
 #pragma unroll
@@ -235,21 +249,21 @@ cross_attention_kernel(const act_t* __restrict__ q, const act_t* __restrict__ kv
     }
     const float inv = 1.0f / sum;
     const float* vh = s_kv + (XD + h * XDH) * 64;
-#pragma unroll 4
+#pragma unroll 2
     for (int c = 0; c < XDH; ++c) {
         const float4* row = reinterpret_cast<const float4*>(vh + c * 64);
-        float a = 0.0f;
+        float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
 #pragma unroll
         for (int k4 = 0; k4 < 16; ++k4) {
             const float4 vv = row[k4];
-            a = fmaf(s[4 * k4 + 0], vv.x, a);
-            a = fmaf(s[4 * k4 + 1], vv.y, a);
-            a = fmaf(s[4 * k4 + 2], vv.z, a);
-            a = fmaf(s[4 * k4 + 3], vv.w, a);
+            a0 = fmaf(s[4 * k4 + 0], vv.x, a0);
+            a1 = fmaf(s[4 * k4 + 1], vv.y, a1);
+            a2 = fmaf(s[4 * k4 + 2], vv.z, a2);
+            a3 = fmaf(s[4 * k4 + 3], vv.w, a3);
         }
 #pragma unroll
-        for (int t = 0; t < XCTX; ++t) a = fmaf(s[64 + t], s_c[t * 384 + XD + h * XDH + c], a);
-        att[(static_cast<size_t>(n2) * XD + h * XDH + c) * 64 + sq] = float_to_act(a * inv);
+        for (int t = 0; t < XCTX; ++t) a0 = fmaf(s[64 + t], s_c[t * 384 + XD + h * XDH + c], a0);
+        att[(static_cast<size_t>(n2) * XD + h * XDH + c) * 64 + sq] = float_to_act(((a0 + a1) + (a2 + a3)) * inv);
     }
 }
 
@@ -269,7 +283,7 @@ void launch_token_layernorm(const act_t* x, const float* g1, const float* b1, ac
 }
 void launch_context_kv(const float* ctx, const float* g, const float* b, const float* wkv_t,
                        const float* bkv, float* ckv, int n, cudaStream_t s) {
-    if (n > 0) context_kv_kernel<<<n, 384, 0, s>>>(ctx, g, b, wkv_t, bkv, ckv);
+    if (n > 0) context_kv_kernel<<<(n + CKV_POS - 1) / CKV_POS, 384, 0, s>>>(ctx, g, b, wkv_t, bkv, ckv, n);
 }
 bool xboard_prepare() {
     return cudaFuncSetAttribute(cross_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
