@@ -481,6 +481,7 @@ static bool add_trunk_run(Worker& w, std::vector<Op>& ops, const Net& net, int f
     p.sums = sums;
     p.trace = nullptr;
     p.dbg = 0;
+    if (const char* dbg = getenv("HM_TRUNK_DBG")) p.dbg = atoi(dbg);  // timing experiments only (wrong results)
     const int grid = n_pos / 2;
     const CUtensorMap tw1 = net.tm_w1, tw2 = net.tm_w2;
     w.trunk_runs.push_back(std::make_shared<TrunkRun>(TrunkRun{p, tm_x, tw1, tw2, grid}));

@@ -85,8 +85,8 @@ enum {
     TB_X_READY,                               // 3
     TB_D2_FULL = TB_X_READY + 3,              // 3
     TB_PAIR_FULL = TB_D2_FULL + 3,            // TR_PAIRS
-    TB_PAIR_EMPTY = TB_PAIR_FULL + TR_PAIRS,  // TR_PAIRS
-    TB_ECA_DONE = TB_PAIR_EMPTY + TR_PAIRS,   // TR_PAIRS: compute warps finished reading a Wc tile pair
+    TB_TILE_EMPTY = TB_PAIR_FULL + TR_PAIRS,  // TR_SLOTS: per 16 KB tile, so its reload starts after ITS 4 MMAs
+    TB_ECA_DONE = TB_TILE_EMPTY + TR_SLOTS,   // TR_PAIRS: compute warps finished reading a Wc tile pair
     TB_COUNT = TB_ECA_DONE + TR_PAIRS
 };
 
@@ -124,6 +124,53 @@ __device__ __forceinline__ void dw_board(const float (&y)[64], const float (&w)[
     }
 }
 
+// The same with packed fp32 FMAs (FFMA2, fma.rn.f32x2): two horizontally adjacent squares per
+// instruction, identical fp32 products.  Every operand is an ALIGNED input pair
+// A[a] = (in[2a], in[2a+1]) (no register shuffling): taps with an even horizontal offset
+// accumulate into the aligned output pairs E[j] = (o[2j], o[2j+1]), taps with an odd offset into
+// the odd-aligned pairs O[k] = (o[2k-1], o[2k]); one scalar add per square joins them.  This
+// cuts the issue slots of the depthwise by ~1/3 (3x3) to ~40 % (5x5) — the FMA-pipe time is the
+// same — which is what the TMA-producer and MMA-issuer warps on the same sub-partitions compete
+// for with the compute warps.
+template <int KS>
+__device__ __forceinline__ void dw_board2(const float (&y)[64], const float (&w)[KS * KS], float bd,
+                                          uint32_t (&packed)[32]) {
+    constexpr int H = KS / 2;
+#pragma unroll
+    for (int yo = 0; yo < 8; ++yo) {
+        float2 E[4], O[5];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) E[j] = make_float2(bd, bd);
+#pragma unroll
+        for (int j = 0; j < 5; ++j) O[j] = make_float2(0.0f, 0.0f);
+#pragma unroll
+        for (int ky = 0; ky < KS; ++ky) {
+            const int yy = yo + ky - H;
+            if (yy < 0 || yy > 7) continue;
+#pragma unroll
+            for (int kx = 0; kx < KS; ++kx) {
+                const int dx = kx - H;
+                const float2 ww = make_float2(w[ky * KS + kx], w[ky * KS + kx]);
+#pragma unroll
+                for (int a = 0; a < 4; ++a) {
+                    const float2 in = make_float2(y[yy * 8 + 2 * a], y[yy * 8 + 2 * a + 1]);
+                    if ((dx & 1) == 0) {
+                        const int j = a - dx / 2;          // o[x] += w * in[x + dx]
+                        if (j < 0 || j > 3) continue;
+                        E[j] = __ffma2_rn(in, ww, E[j]);
+                    } else {
+                        const int k = a + (1 - dx) / 2;    // pair (o[2a-dx], o[2a+1-dx]) = O[k]
+                        O[k] = __ffma2_rn(in, ww, O[k]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            packed[yo * 4 + j] = pack_act2_relu(E[j].x + O[j].y, E[j].y + O[j + 1].x);
+    }
+}
+
 // Per-thread parameters of one 128-channel chunk: pw1 bias, depthwise bias, k*k depthwise taps.
 template <int KS>
 struct ChunkPar {
@@ -144,7 +191,8 @@ template <int KS>
 __device__ __forceinline__ void trunk_chunk(ChunkPar<KS>& cur, const float* __restrict__ par_next,
                                             int r, uint32_t tm_d1, uint64_t* bars, uint32_t d1_n,
                                             uint32_t z_n, uint8_t* zrow, int lane,
-                                            unsigned long long* tr_trace, int& trace_n, int dbg) {
+                                            unsigned long long* tr_trace, int& trace_n, int dbg,
+                                            long long* prof) {
     float y[64];
     TR_MARK(2, 1);
     tr_wait_full(&bars[TB_D1_FULL], d1_n);
@@ -158,10 +206,15 @@ __device__ __forceinline__ void trunk_chunk(ChunkPar<KS>& cur, const float* __re
         tmem_ld_32x32b_x32(tm_d1, a0);
         tmem_ld_32x32b_x32(tm_d1 + 32, a1);
         tmem_ld_wait();
+        const float2 bb = make_float2(cur.b1, cur.b1);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            y[j] = fmaxf(__uint_as_float(a0[j]) + cur.b1, 0.0f);
-            y[32 + j] = fmaxf(__uint_as_float(a1[j]) + cur.b1, 0.0f);
+        for (int j = 0; j < 16; ++j) {   // packed bias add (FADD2), scalar max
+            const float2 u = __fadd2_rn(make_float2(__uint_as_float(a0[2 * j]), __uint_as_float(a0[2 * j + 1])), bb);
+            const float2 v = __fadd2_rn(make_float2(__uint_as_float(a1[2 * j]), __uint_as_float(a1[2 * j + 1])), bb);
+            y[2 * j] = fmaxf(u.x, 0.0f);
+            y[2 * j + 1] = fmaxf(u.y, 0.0f);
+            y[32 + 2 * j] = fmaxf(v.x, 0.0f);
+            y[32 + 2 * j + 1] = fmaxf(v.y, 0.0f);
         }
     }
     tc_fence_before();
@@ -174,8 +227,24 @@ __device__ __forceinline__ void trunk_chunk(ChunkPar<KS>& cur, const float* __re
     if ((dbg & 1) || ((dbg & 8) && ((threadIdx.x >> 5) & 3) < 2) || ((dbg & 16) && ((threadIdx.x >> 5) & 3) >= 2)) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) packed[j] = __float_as_uint(y[2 * j]);
+    } else if (dbg & 32) {
+        // experiment: the same number of FFMAs as the depthwise from a ROLLED loop (tiny code
+        // footprint) -> separates issue-slot pressure from instruction-cache pressure
+        float a[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = y[j];
+#pragma unroll 1
+        for (int it = 0; it < (KS == 3 ? 60 : 144); ++it) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = fmaf(a[j], cur.w[j], y[8 + j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) packed[j] = __float_as_uint(a[j & 7] + y[2 * j]);
     } else {
-        dw_board<KS>(y, cur.w, cur.bd, packed);
+        const long long t0 = prof ? clock64() : 0;
+        if (dbg & 64) dw_board<KS>(y, cur.w, cur.bd, packed);   // scalar FFMA variant kept for A/B timing
+        else dw_board2<KS>(y, cur.w, cur.bd, packed);
+        if (prof) *prof += clock64() - t0;
     }
     TR_MARK(2, 4);
     tr_wait_empty(&bars[TB_Z_EMPTY], z_n);  // pw2 of the previous chunk has consumed Z
@@ -199,12 +268,13 @@ template <int KS>
 __device__ __forceinline__ void trunk_block_chunks(const float* __restrict__ par0, int nch, int r,
                                                    uint32_t tm_d1, uint64_t* bars, uint32_t& d1_n,
                                                    uint32_t& z_n, uint8_t* zrow, int lane,
-                                                   unsigned long long* tr_trace, int& trace_n, int dbg) {
+                                                   unsigned long long* tr_trace, int& trace_n, int dbg,
+                                                   long long* prof) {
     ChunkPar<KS> cur;
     cur.load(par0, r);
     for (int c = 0; c < nch; ++c) {
         const float* nxt = (c + 1 < nch) ? par0 + static_cast<size_t>(c + 1) * TR_PAR_FLOATS : nullptr;
-        trunk_chunk<KS>(cur, nxt, r, tm_d1, bars, d1_n, z_n, zrow, lane, tr_trace, trace_n, dbg);
+        trunk_chunk<KS>(cur, nxt, r, tm_d1, bars, d1_n, z_n, zrow, lane, tr_trace, trace_n, dbg, prof);
         ++d1_n;
         ++z_n;
     }
@@ -268,16 +338,17 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             TR_MARK(0, 1);
 #pragma unroll
             for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
-                mbar_wait(&bars[TB_PAIR_EMPTY + b2], par);
-                TR_MARK(0, 10 + b2);
-                if (leader) {
-                    mbar_arrive_expect_tx(&bars[TB_PAIR_FULL + b2], 2 * TR_SLOT_BYTES);
 #pragma unroll
-                    for (int j = 0; j < 2; ++j)
+                for (int j = 0; j < 2; ++j) {
+                    mbar_wait(&bars[TB_TILE_EMPTY + 2 * b2 + j], par);
+                    if (j == 0) TR_MARK(0, 10 + b2);
+                    if (leader) {
+                        if (j == 0) mbar_arrive_expect_tx(&bars[TB_PAIR_FULL + b2], 2 * TR_SLOT_BYTES);
                         tma_load_2d(smem + TR_RING_OFF + (2 * b2 + j) * TR_SLOT_BYTES, &tmW1,
                                     &bars[TB_PAIR_FULL + b2], (2 * b2 + j) * 64, g * 128);
+                    }
+                    __syncwarp();
                 }
-                __syncwarp();
             }
             par ^= 1;
         };
@@ -285,16 +356,17 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             TR_MARK(0, 2);
 #pragma unroll
             for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
-                mbar_wait(&bars[TB_PAIR_EMPTY + b2], par);
-                TR_MARK(0, 20 + b2);
-                if (leader) {
-                    mbar_arrive_expect_tx(&bars[TB_PAIR_FULL + b2], 2 * TR_SLOT_BYTES);
 #pragma unroll
-                    for (int j = 0; j < 2; ++j)   // pair b2 = output block m = b2, K halves kh = j
+                for (int j = 0; j < 2; ++j) {   // pair b2 = output block m = b2, K halves kh = j
+                    mbar_wait(&bars[TB_TILE_EMPTY + 2 * b2 + j], par);
+                    if (j == 0) TR_MARK(0, 20 + b2);
+                    if (leader) {
+                        if (j == 0) mbar_arrive_expect_tx(&bars[TB_PAIR_FULL + b2], 2 * TR_SLOT_BYTES);
                         tma_load_2d(smem + TR_RING_OFF + (2 * b2 + j) * TR_SLOT_BYTES, &tmW2,
                                     &bars[TB_PAIR_FULL + b2], j * 64, g * 384 + b2 * 128);
+                    }
+                    __syncwarp();
                 }
-                __syncwarp();
             }
             par ^= 1;
         };
@@ -340,8 +412,8 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                         for (int k = 0; k < 4; ++k)
                             umma_f16_lh(tm_d1, a0 + (kb * 1024 + 2 * k), a_hi, xd0 + (kb * 1024 + k * 128), b_hi,
                                         idesc, (kb | k) ? 1u : 0u);
+                        umma_commit(&bars[TB_TILE_EMPTY + kb]);
                     }
-                    umma_commit(&bars[TB_PAIR_EMPTY + b2]);
                     if (b2 == TR_PAIRS - 1) umma_commit(&bars[TB_D1_FULL]);
                 }
                 __syncwarp();
@@ -359,7 +431,10 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
 #pragma unroll
                     for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
                         tr_wait_full(&bars[TB_ECA_DONE + b2], eca_n);
-                        if (leader) mbar_arrive(&bars[TB_PAIR_EMPTY + b2]);
+                        if (leader) {
+                            mbar_arrive(&bars[TB_TILE_EMPTY + 2 * b2]);
+                            mbar_arrive(&bars[TB_TILE_EMPTY + 2 * b2 + 1]);
+                        }
                         __syncwarp();
                     }
                     par ^= 1;
@@ -387,8 +462,8 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                             for (int k = 0; k < 4; ++k)
                                 umma_f16_lh(tm_d2 + m * 128, a0 + ((2 * m + kh) * 1024 + 2 * k), a_hi,
                                             zd0 + (kh * 1024 + k * 128), b_hi, idesc, (kh | k) ? 1u : acc0);
+                            umma_commit(&bars[TB_TILE_EMPTY + 2 * m + kh]);
                         }
-                        umma_commit(&bars[TB_PAIR_EMPTY + m]);
                         if (last_chunk) umma_commit(&bars[TB_D2_FULL + m]);  // output block m complete
                         if (m == TR_PAIRS - 1) umma_commit(&bars[TB_Z_EMPTY]);
                     }
@@ -441,6 +516,8 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         uint32_t d1_n = 0, z_n = 0, gcount = 0;   // gcount = ring groups (laps) so far
         int trace_n = 0;
         unsigned long long* const ctrace = warp == 2 ? tr_trace : nullptr;
+        long long math_cycles = 0;   // per-warp total of the depthwise math (tracing only)
+        long long* const prof = (blockIdx.x == 0 && p.trace != nullptr) ? &math_cycles : nullptr;
         float* const zmean = reinterpret_cast<float*>(smem + TR_Z_OFF);  // [2 pos][384] while Z is idle
         for (int b = 0; b < p.n_blocks; ++b) {
             const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks, ks = p.blk[b].ksize;
@@ -502,9 +579,9 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 const float* par0 = p.par + static_cast<size_t>(g0) * TR_PAR_FLOATS;
                 uint8_t* zrow = smem + TR_Z_OFF + row_off;
                 if (ks == 3)
-                    trunk_block_chunks<3>(par0, nch, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane, ctrace, trace_n, p.dbg);
+                    trunk_block_chunks<3>(par0, nch, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane, ctrace, trace_n, p.dbg, prof);
                 else
-                    trunk_block_chunks<5>(par0, nch, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane, ctrace, trace_n, p.dbg);
+                    trunk_block_chunks<5>(par0, nch, r, tm_d1 + lane_off + h * 64, bars, d1_n, z_n, zrow, lane, ctrace, trace_n, p.dbg, prof);
             }
             // ---- block epilogue: x <- x + D2 + b2, in place in shared memory ----
             const bool last = (b + 1 == p.n_blocks);
@@ -560,6 +637,9 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 named_bar_sync(2, TR_COMPUTE);
             }
         }
+        if (prof != nullptr && lane == 0)   // tail of role 2's region: tag 100 + warp
+            p.trace[3 * TR_TRACE_CAP - 16 + warp] =
+                (static_cast<unsigned long long>(100 + warp) << 48) | (static_cast<unsigned long long>(math_cycles) & 0xffffffffffffull);
         // ---- run output: shared-memory tile -> global (TMA store) ----
         named_bar_sync(1, TR_COMPUTE);
         if (threadIdx.x == 64) {

@@ -39,7 +39,7 @@ class ForwardOracle:
             self.n_blocks += 1
 
     @torch.no_grad()
-    def forward(self, planes: np.ndarray, return_intermediates: bool = False):
+    def forward(self, planes: np.ndarray, return_intermediates: bool = False, trunk_override=None):
         """planes: [B,74,8,8] float32.  Returns dict(value[B], wdl[B,3], moves_left[B],
         pi_a[B,4672], pi_b[B,4672]) as float32 numpy arrays."""
         t = self.t
@@ -64,6 +64,8 @@ class ForwardOracle:
             y = F.conv2d(y, t[q + "pw2.w"][:, :, None, None], t[q + "pw2.b"])
             x = x + y  # builder_util.py:483, no activation after the add
             inter[f"block{i}"] = x
+        if trunk_override is not None:   # error attribution: heads in fp32 on a given trunk output
+            x = _t(trunk_override)
         cross = "tok0.wt" in t
         if cross:
             maps = self._crossboard(_t(planes), x, inter)

@@ -55,6 +55,11 @@ def main():
     stats("value", raw[:, 0], ref["value"])
     stats("wdl", raw[:, 1:4], ref["wdl"])
     stats("moves_left", raw[:, 4], ref["moves_left"])
+    # error attribution: fp32 oracle heads on OUR trunk output
+    ours_trunk = eng.debugFetch("trunk").reshape(n, 384, 8, 8)
+    mixed = ForwardOracle(folded).forward(planes, trunk_override=ours_trunk)
+    stats("value|our trunk", mixed["value"], ref["value"])
+    stats("value vs mixed", raw[:, 0], mixed["value"])
     kls = []
     for i in range(n):
         for bn in range(2):

@@ -42,6 +42,11 @@ def main():
         tr = eng.traceTrunk(run)
         tr = eng.traceTrunk(run)
         print(f"==== trunk run {run}")
+        warp_math = {tag - 100: t for tag, t in tr[2] if tag >= 100}
+        tr[2] = [(tag, t) for tag, t in tr[2] if tag < 100]
+        if warp_math:
+            print("   depthwise math cycles per compute warp (warp: SP = warp % 4): " +
+                  ", ".join(f"w{w}(SP{w % 4}) {c}" for w, c in sorted(warp_math.items())))
         summarize("producer", tr[0], {}, [(1, 2, "W1 group -> next W2 group issue"), (2, 1, "W2 group -> next W1 group"), (2, 2, "W2 -> W2")])
         summarize("mma", tr[1], MMA, [(1, 2, "wait D1_EMPTY"), (2, 3, "pw1 issue (6 tiles, waits ring)"), (4, 5, "wait Z_FULL"), (5, 6, "pw2 issue (6 tiles)"),
                                       (3, 4, "pw1 end -> pw2 begin"), (6, 1, "pw2 end -> pw1 begin")])
