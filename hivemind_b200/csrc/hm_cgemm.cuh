@@ -44,13 +44,19 @@ struct CgemmParams {
 };
 
 constexpr int CG_THREADS = 192;
-constexpr int CG_STAGES = 3;
-// One stage = 128 K values: two A tiles (2 x 16 KB) + two B blocks (2 x 16 KB) behind ONE barrier
-// pair, i.e. 8 MMAs (512 tensor-pipe cycles) per barrier round trip of the single-thread producer
-// and issuer loops (a 4-MMA stage cannot hide it: tools/probes/probe_mmaring.cu).
-constexpr int CG_STAGE_BYTES = 65536;
-constexpr int CG_SMEM = CG_STAGES * CG_STAGE_BYTES + 256 + 1024;
-constexpr int cg_smem_bytes(int stages) { return stages * CG_STAGE_BYTES + 256 + 1024; }
+// Shared memory: a ring of WEIGHT stages (two 16 KB A tiles = 128 K values of 128 output
+// channels) and a ring of ACTIVATION stages (two 16 KB B blocks = 128 channels x 2 positions).
+// For a 3x3 convolution one activation stage serves the three horizontal taps kx (they differ
+// only in the weights and in the accumulator, the horizontal shift happens in the epilogue), so
+// the activation tile crosses L2->SM once per (ky, 128 channels) instead of three times: the
+// per-SM L2 ingest (~52-62 B/clk measured, tools/probes/probe_mmaring.cu) is what bounds these
+// layers, not the tensor pipe.  8 MMAs (512 tensor-pipe cycles) per weight-barrier round trip.
+constexpr int CG_WSTAGES = 4;
+constexpr int CG_XSTAGES = 2;
+constexpr int CG_STAGE_BYTES = 32768;
+constexpr int CG_STAGES = 3;   // legacy name: default ring depth handed to CgemmParams::stages
+constexpr int cg_smem_bytes(int wstages, int xstages) { return (wstages + xstages) * CG_STAGE_BYTES + 256 + 1024; }
+constexpr int CG_SMEM = cg_smem_bytes(CG_WSTAGES, CG_XSTAGES);
 
 __global__ void __launch_bounds__(CG_THREADS)
 cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
@@ -58,10 +64,15 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
     extern __shared__ uint8_t cg_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cg_smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
-    const int n_stages = p.stages;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + n_stages * CG_STAGE_BYTES);
-    uint64_t* empty_bar = full_bar + CG_STAGES;
-    uint64_t* accum_bar = empty_bar + CG_STAGES;
+    // stages == 1: shallow-K 1x1 layers run with one W and one X stage so that 3 CTAs share an SM
+    const int n_w = p.stages == 1 ? 1 : CG_WSTAGES;
+    const int n_x = p.stages == 1 ? 1 : CG_XSTAGES;
+    uint8_t* smem_x = smem + n_w * CG_STAGE_BYTES;
+    uint64_t* full_w = reinterpret_cast<uint64_t*>(smem_x + n_x * CG_STAGE_BYTES);
+    uint64_t* empty_w = full_w + CG_WSTAGES;
+    uint64_t* full_x = empty_w + CG_WSTAGES;
+    uint64_t* empty_x = full_x + CG_XSTAGES;
+    uint64_t* accum_bar = empty_x + CG_XSTAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
 
     const int warp = threadIdx.x >> 5;
@@ -72,9 +83,13 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmW);
         tma_prefetch_desc(&tmX);
-        for (int s = 0; s < n_stages; ++s) {
-            mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], 1);
+        for (int s = 0; s < CG_WSTAGES; ++s) {
+            mbar_init(&full_w[s], 1);
+            mbar_init(&empty_w[s], 1);
+        }
+        for (int s = 0; s < CG_XSTAGES; ++s) {
+            mbar_init(&full_x[s], 1);
+            mbar_init(&empty_x[s], 1);
         }
         mbar_init(accum_bar, 1);
         fence_barrier_init();
@@ -93,24 +108,33 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
     // both single-thread roles run warp-uniform; only the issuing instructions are predicated
     if (warp == 0) {
         const bool leader = elect_one();
-        int stage = 0, kcol = 0;
-        uint32_t phase = 1;
+        int ws = 0, xs = 0;
+        uint32_t wphase = 1, xphase = 1;
         const int row0 = mb * 128, pos0 = tile * 2;
+        const int tap_cols = p.kblocks * 64;            // K columns of one tap in the weight matrix
         for (int ky = 0; ky < p.ksize; ++ky) {
             const int sq0 = 8 * (ky - (p.ksize >> 1));   // vertical tap offset as a square shift
-            for (int kx = 0; kx < p.ksize; ++kx) {
-                for (int kp = 0; kp < kpairs; ++kp, kcol += 128) {
-                    mbar_wait(&empty_bar[stage], phase);
+            for (int kp = 0; kp < kpairs; ++kp) {
+                mbar_wait(&empty_x[xs], xphase);
+                if (leader) {
+                    uint8_t* dst = smem_x + xs * CG_STAGE_BYTES;
+                    mbar_arrive_expect_tx(&full_x[xs], CG_STAGE_BYTES);
+                    tma_load_3d(dst, &tmX, &full_x[xs], sq0, kp * 128, pos0);
+                    tma_load_3d(dst + 16384, &tmX, &full_x[xs], sq0, kp * 128 + 64, pos0);
+                }
+                __syncwarp();
+                if (++xs == n_x) { xs = 0; xphase ^= 1; }
+                for (int kx = 0; kx < p.ksize; ++kx) {
+                    const int kcol = (ky * p.ksize + kx) * tap_cols + kp * 128;
+                    mbar_wait(&empty_w[ws], wphase);
                     if (leader) {
-                        uint8_t* dst = smem + stage * CG_STAGE_BYTES;
-                        mbar_arrive_expect_tx(&full_bar[stage], CG_STAGE_BYTES);
-                        tma_load_2d(dst, &tmW, &full_bar[stage], kcol, row0);
-                        tma_load_2d(dst + 16384, &tmW, &full_bar[stage], kcol + 64, row0);
-                        tma_load_3d(dst + 32768, &tmX, &full_bar[stage], sq0, kp * 128, pos0);
-                        tma_load_3d(dst + 49152, &tmX, &full_bar[stage], sq0, kp * 128 + 64, pos0);
+                        uint8_t* dst = smem + ws * CG_STAGE_BYTES;
+                        mbar_arrive_expect_tx(&full_w[ws], CG_STAGE_BYTES);
+                        tma_load_2d(dst, &tmW, &full_w[ws], kcol, row0);
+                        tma_load_2d(dst + 16384, &tmW, &full_w[ws], kcol + 64, row0);
                     }
                     __syncwarp();
-                    if (++stage == n_stages) { stage = 0; phase ^= 1; }
+                    if (++ws == n_w) { ws = 0; wphase ^= 1; }
                 }
             }
         }
@@ -118,30 +142,34 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
         const bool leader = elect_one();
         constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
         const uint64_t a0 = umma_desc_sw128(smem_u32(smem));
-        const uint64_t b0 = umma_desc_mn_sw128(smem_u32(smem) + 32768, 8192, 1024);
-        int stage = 0;
-        uint32_t phase = 0;
+        const uint64_t b0 = umma_desc_mn_sw128(smem_u32(smem_x), 8192, 1024);
+        int ws = 0, xs = 0;
+        uint32_t wphase = 0, xphase = 0;
         for (int ky = 0; ky < p.ksize; ++ky) {
-            for (int kx = 0; kx < p.ksize; ++kx) {       // accumulator = horizontal offset kx
-                const uint32_t d = tmem_base + kx * 128;
-                for (int kp = 0; kp < kpairs; ++kp) {
-                    mbar_wait(&full_bar[stage], phase);
+            for (int kp = 0; kp < kpairs; ++kp) {
+                mbar_wait(&full_x[xs], xphase);
+                const uint32_t xo = xs * (CG_STAGE_BYTES / 16);
+                for (int kx = 0; kx < p.ksize; ++kx) {       // accumulator = horizontal offset kx
+                    const uint32_t d = tmem_base + kx * 128;
+                    mbar_wait(&full_w[ws], wphase);
                     tc_fence_after();
                     if (leader) {
-                        const uint32_t so = stage * (CG_STAGE_BYTES / 16);
+                        const uint32_t wo = ws * (CG_STAGE_BYTES / 16);
                         const uint32_t acc0 = (ky | kp) ? 1u : 0u;  // first tile of this accumulator
 #pragma unroll
                         for (int j = 0; j < 2; ++j) {
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
-                                umma_f16(d, a0 + (so + j * 1024 + 2 * k), b0 + (so + j * 1024 + k * 128), idesc,
+                                umma_f16(d, a0 + (wo + j * 1024 + 2 * k), b0 + (xo + j * 1024 + k * 128), idesc,
                                          (j | k) ? 1u : acc0);
                         }
-                        umma_commit(&empty_bar[stage]);
+                        umma_commit(&empty_w[ws]);
+                        if (kx == p.ksize - 1) umma_commit(&empty_x[xs]);
                     }
                     __syncwarp();
-                    if (++stage == n_stages) { stage = 0; phase ^= 1; }
+                    if (++ws == n_w) { ws = 0; wphase ^= 1; }
                 }
+                if (++xs == n_x) { xs = 0; xphase ^= 1; }
             }
         }
         if (leader) umma_commit(accum_bar);

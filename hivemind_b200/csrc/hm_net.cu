@@ -527,7 +527,7 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
     // a 1x1 layer has only Cpad/128 <= 3 stage loads per CTA: a deep ring buys nothing, three
     // co-resident CTAs (64 KB each, 128 TMEM columns) overlap one CTA's epilogue with another's MMAs
     p.stages = L.ksize == 1 ? 1 : CG_STAGES;
-    const int smem = cg_smem_bytes(p.stages);
+    const int smem = p.stages == 1 ? cg_smem_bytes(1, 1) : CG_SMEM;
     const int grid = (io.in_n / 2) * p.m_blocks;
     const CUtensorMap tm_w = L.tm_w;
     Op op;
