@@ -204,15 +204,19 @@ __device__ __forceinline__ void trunk_chunk(ChunkPar<KS>& cur, const float* __re
     } else {
         uint32_t a0[32], a1[32];
         tmem_ld_32x32b_x32(tm_d1, a0);
-        tmem_ld_32x32b_x32(tm_d1 + 32, a1);
         tmem_ld_wait();
+        tmem_ld_32x32b_x32(tm_d1 + 32, a1);   // streams out while the first half is prepared
         const float2 bb = make_float2(cur.b1, cur.b1);
 #pragma unroll
         for (int j = 0; j < 16; ++j) {   // packed bias add (FADD2), scalar max
             const float2 u = __fadd2_rn(make_float2(__uint_as_float(a0[2 * j]), __uint_as_float(a0[2 * j + 1])), bb);
-            const float2 v = __fadd2_rn(make_float2(__uint_as_float(a1[2 * j]), __uint_as_float(a1[2 * j + 1])), bb);
             y[2 * j] = fmaxf(u.x, 0.0f);
             y[2 * j + 1] = fmaxf(u.y, 0.0f);
+        }
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const float2 v = __fadd2_rn(make_float2(__uint_as_float(a1[2 * j]), __uint_as_float(a1[2 * j + 1])), bb);
             y[32 + 2 * j] = fmaxf(v.x, 0.0f);
             y[32 + 2 * j + 1] = fmaxf(v.y, 0.0f);
         }
@@ -592,36 +596,45 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
 #pragma unroll
             for (int m = 0; m < 3; ++m) {
                 const float bias = __ldg(b2 + m * 128 + r);
+                uint8_t* xrow = smem + TR_X_OFF + m * 32768 + row_off;
+                uint4 res[8];   // residual row: independent of D2, fetched before the wait
+#pragma unroll
+                for (int j = 0; j < 8; ++j) res[j] = *reinterpret_cast<const uint4*>(xrow + ((j ^ key) << 4));
                 { unsigned long long* tr_trace = ctrace; TR_MARK(2, 7); }
                 tr_wait_full(&bars[TB_D2_FULL + m], b);
                 tc_fence_after();
                 { unsigned long long* tr_trace = ctrace; TR_MARK(2, 8); }
+                // the second half of the accumulator row streams out of TMEM while the first is processed
                 uint32_t a0[32], a1[32];
                 tmem_ld_32x32b_x32(tm_d2 + lane_off + m * 128 + h * 64, a0);
-                tmem_ld_32x32b_x32(tm_d2 + lane_off + m * 128 + h * 64 + 32, a1);
-                uint8_t* xrow = smem + TR_X_OFF + m * 32768 + row_off;
                 tmem_ld_wait();
-                float s = 0.0f;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    uint4* px = reinterpret_cast<uint4*>(xrow + ((j ^ key) << 4));
-                    const uint4 v = *px;
+                tmem_ld_32x32b_x32(tm_d2 + lane_off + m * 128 + h * 64 + 32, a1);
+                const float2 bb = make_float2(bias, bias);
+                float s = 0.0f, s1 = 0.0f;
+                auto piece = [&](int j, const uint32_t (&a)[32], int base) {
+                    const uint4 v = res[j];
                     const uint32_t ru[4] = {v.x, v.y, v.z, v.w};
                     uint32_t ou[4];
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        const int i = j * 8 + e * 2;
-                        const float2 res = unpack_act2(ru[e]);
-                        const float v0 = __uint_as_float(i < 32 ? a0[i] : a1[i - 32]) + bias + res.x;
-                        const float v1 = __uint_as_float(i < 32 ? a0[i + 1] : a1[i - 31]) + bias + res.y;
-                        ou[e] = pack_act2(v0, v1);
+                        const int i = j * 8 + e * 2 - base;
+                        const float2 acc = __fadd2_rn(make_float2(__uint_as_float(a[i]), __uint_as_float(a[i + 1])), bb);
+                        const float2 o = __fadd2_rn(acc, unpack_act2(ru[e]));
+                        ou[e] = pack_act2(o.x, o.y);
                         if (want_sums) {  // ECA squeeze of the next run: sum of what was actually stored
                             const float2 rd = unpack_act2(ou[e]);
-                            s += rd.x + rd.y;
+                            s += rd.x;
+                            s1 += rd.y;
                         }
                     }
-                    *px = make_uint4(ou[0], ou[1], ou[2], ou[3]);
-                }
+                    *reinterpret_cast<uint4*>(xrow + ((j ^ key) << 4)) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
+                };
+#pragma unroll
+                for (int j = 0; j < 4; ++j) piece(j, a0, 0);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 4; j < 8; ++j) piece(j, a1, 32);
+                s += s1;
                 sums3[m] = s;
                 if (last && p.sums != nullptr) p.sums[static_cast<size_t>(pos) * 384 + m * 128 + r] = s;
                 tc_fence_before();

@@ -80,7 +80,8 @@ __global__ void __launch_bounds__(128, 1) mmaring(const __grid_constant__ CUtens
 template <int SLOTS, int GROUP>
 __global__ void __launch_bounds__(128, 1) mmaring_fast(const __grid_constant__ CUtensorMap tm, int n_laps, int rows_total,
                                                        long long* cycles_out, int stagger, int mode,
-                                                       const __grid_constant__ CUtensorMap tm2, const uint8_t* flat) {
+                                                       const __grid_constant__ CUtensorMap tm2, const uint8_t* flat,
+                                                       const __grid_constant__ CUtensorMap tm3) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* bop = smem;
     uint8_t* ringp = smem + 16384;
@@ -115,7 +116,8 @@ __global__ void __launch_bounds__(128, 1) mmaring_fast(const __grid_constant__ C
 #pragma unroll
                     for (int j = 0; j < GROUP; ++j) {
                         const int s = b * GROUP + j;
-                        if (mode == 1) tma_load_2d(ringp + s * 16384, &tm2, &full[b], (s & 1) * 64, (rb * 3 + (s >> 1)) * 128);
+                        if (mode == 3) tma_load_2d(ringp + s * 16384, &tm3, &full[b], 0, (rb * 6 + s) * 128);
+                        else if (mode == 1) tma_load_2d(ringp + s * 16384, &tm2, &full[b], (s & 1) * 64, (rb * 3 + (s >> 1)) * 128);
                         else tma_load_2d(ringp + s * 16384, &tm, &full[b], (s % 6) * 64, rb * 128);
                     }
                 }
@@ -152,15 +154,15 @@ __global__ void __launch_bounds__(128, 1) mmaring_fast(const __grid_constant__ C
     __syncthreads();
     if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 128); }
 }
-static CUtensorMap g_tm2;
+static CUtensorMap g_tm2, g_tm3;
 static const uint8_t* g_flat;
 template <int SLOTS, int GROUP>
 static void run_fast(const CUtensorMap& tm, int rows, long long* dc) {
     cudaFuncSetAttribute(mmaring_fast<SLOTS, GROUP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 13 * 16384 + 1024);
     const int n_laps = 2400 / SLOTS;
-    for (int mode : {0, 1, 2}) for (int stagger : {0}) for (int grid : {148}) {
+    for (int mode : {0, 1, 2, 3}) for (int stagger : {0}) for (int grid : {148}) {
         for (int rep = 0; rep < 2; ++rep) {
-            mmaring_fast<SLOTS, GROUP><<<grid, 128, (SLOTS + 1) * 16384 + 1024>>>(tm, n_laps, rows, dc, stagger, mode, g_tm2, g_flat);
+            mmaring_fast<SLOTS, GROUP><<<grid, 128, (SLOTS + 1) * 16384 + 1024>>>(tm, n_laps, rows, dc, stagger, mode, g_tm2, g_flat, g_tm3);
             cudaError_t e = cudaDeviceSynchronize();
             if (e != cudaSuccess) { printf("err %s\n", cudaGetErrorString(e)); exit(1); }
         }
@@ -191,6 +193,11 @@ int main() {
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r) { printf("encode2 %d\n", (int)r); return 1; }
         g_flat = reinterpret_cast<const uint8_t*>(d);
+        cuuint64_t d3[2] = {64, (cuuint64_t)rows * 6};
+        cuuint64_t s3[1] = {128};
+        r = cuTensorMapEncodeTiled(&g_tm3, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, d, d3, s3, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r) { printf("encode3 %d\n", (int)r); return 1; }
     }
     long long* dc;
     cudaMalloc(&dc, 1024 * 8);

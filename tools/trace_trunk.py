@@ -62,9 +62,12 @@ def main():
                     d = np.array(mi[:n]) - np.array(pi[:n])
                     print(f"   {nm} pair {b}: load issue -> seen full: mean {d.mean():7.0f} med {np.median(d):7.0f} min {d.min():6d} max {d.max():6d}")
         if os.environ.get("HM_TRACE_DUMP"):
-            for role in range(3):
-                t0 = tr[1][0][1] if tr[1] else 0
-                print(role, [(tag, t - t0) for tag, t in tr[role][:80]])
+            lo = int(os.environ.get("HM_TRACE_DUMP"))
+            t0 = tr[1][0][1] if tr[1] else 0
+            merged = sorted([(t - t0, role, tag) for role in range(3) for tag, t in tr[role]])
+            sel = [e for e in merged if lo <= e[0] < lo + 12000]
+            for t, role, tag in sel:
+                print(f"   t={t:8d} {['producer', 'mma     ', 'compute '][role]} tag {tag}")
     eng.close()
 
 
