@@ -86,8 +86,9 @@ enum {
     TB_D2_FULL = TB_X_READY + 3,              // 3
     TB_PAIR_FULL = TB_D2_FULL + 3,            // TR_PAIRS
     TB_TILE_EMPTY = TB_PAIR_FULL + TR_PAIRS,  // TR_SLOTS: per 16 KB tile, so its reload starts after ITS 4 MMAs
-    TB_ECA_DONE = TB_TILE_EMPTY + TR_SLOTS,   // TR_PAIRS: compute warps finished reading a Wc tile pair
-    TB_COUNT = TB_ECA_DONE + TR_PAIRS
+    TB_ECA_DONE = TB_TILE_EMPTY + TR_SLOTS,   // 3: gate pre-activations of output block m are in TMEM
+    TB_ECA_READY = TB_ECA_DONE + 3,           // the channel means of the block input are in shared memory
+    TB_COUNT = TB_ECA_READY + 1
 };
 
 // k-th completion (k = 0, 1, ...) of a "full"-type barrier
@@ -303,8 +304,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         tma_prefetch_desc(&tmW2);
         for (int i = 0; i < TB_COUNT; ++i) {
             uint32_t count = 1;
-            if ((i >= TB_X_READY && i < TB_X_READY + 3) || i == TB_D1_EMPTY || i == TB_Z_FULL ||
-                (i >= TB_ECA_DONE && i < TB_ECA_DONE + TR_PAIRS))
+            if ((i >= TB_X_READY && i < TB_X_READY + 3) || i == TB_D1_EMPTY || i == TB_Z_FULL || i == TB_ECA_READY)
                 count = 8;
             mbar_init(&bars[i], count);
         }
@@ -397,6 +397,8 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         const uint32_t a0 = static_cast<uint32_t>(a0d), a_hi = static_cast<uint32_t>(a0d >> 32);
         const uint32_t xd0 = static_cast<uint32_t>(xd0d), zd0 = static_cast<uint32_t>(zd0d);
         const uint32_t b_hi = static_cast<uint32_t>(xd0d >> 32);
+        const uint64_t zmd = umma_desc_sw128(smem_u32(smem + TR_Z_OFF));   // ECA means: K-major, 16 rows per K block
+        const uint32_t zm0 = static_cast<uint32_t>(zmd), zm_hi = static_cast<uint32_t>(zmd >> 32);
         auto pw1 = [&](int xblock) {   // xblock >= 0: first pw1 of bottleneck block `xblock`
             TR_MARK(1, 1);
             tr_wait_empty(&bars[TB_D1_EMPTY], d1_n);
@@ -430,20 +432,34 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         for (int b = 0; b < p.n_blocks; ++b) {
             const int nch = p.blk[b].n_chunks;
             if (b > 0 && p.blk[b].eca_chunk0 >= 0) {
-                // the compute warps consume the Wc tiles; hand the ring slots back on their behalf
+                // ECA matvec on the tensor core: G[m] (128 out channels x N = 16, columns 0/1 = the
+                // two positions) = Wc tiles (ring) x channel means (fp16, K-major, parked in the Z
+                // buffer by the compute warps); accumulators in the idle D2 columns
+                constexpr uint32_t idesc_eca = umma_idesc_16(128, 16, UMMA_FMT_16);
+                if (!(p.dbg & 128)) tr_wait_full(&bars[TB_ECA_READY], eca_n);
+                tc_fence_after();
                 for (int m = 0; m < 3; ++m) {
 #pragma unroll
                     for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
-                        tr_wait_full(&bars[TB_ECA_DONE + b2], eca_n);
+                        mbar_wait(&bars[TB_PAIR_FULL + b2], par);
+                        tc_fence_after();
                         if (leader) {
-                            mbar_arrive(&bars[TB_TILE_EMPTY + 2 * b2]);
-                            mbar_arrive(&bars[TB_TILE_EMPTY + 2 * b2 + 1]);
+#pragma unroll
+                            for (int j = 0; j < 2; ++j) {
+                                const int kb = 2 * b2 + j;
+#pragma unroll
+                                for (int k = 0; k < 4; ++k)
+                                    umma_f16_lh(tm_d2 + m * 16, a0 + (kb * 1024 + 2 * k), a_hi, zm0 + (kb * 128 + 2 * k), zm_hi,
+                                                idesc_eca, (kb | k) ? 1u : 0u);
+                                umma_commit(&bars[TB_TILE_EMPTY + kb]);
+                            }
+                            if (b2 == TR_PAIRS - 1) umma_commit(&bars[TB_ECA_DONE + m]);
                         }
                         __syncwarp();
                     }
                     par ^= 1;
-                    ++eca_n;
                 }
+                ++eca_n;
             }
             pw1(b);
             for (int c = 0; c < nch; ++c) {
@@ -517,48 +533,32 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             mbar_arrive(&bars[TB_X_READY + 2]);
         }
 
-        uint32_t d1_n = 0, z_n = 0, gcount = 0;   // gcount = ring groups (laps) so far
+        uint32_t d1_n = 0, z_n = 0, eca_cnt = 0;
         int trace_n = 0;
         unsigned long long* const ctrace = warp == 2 ? tr_trace : nullptr;
         long long math_cycles = 0;   // per-warp total of the depthwise math (tracing only)
         long long* const prof = (blockIdx.x == 0 && p.trace != nullptr) ? &math_cycles : nullptr;
-        float* const zmean = reinterpret_cast<float*>(smem + TR_Z_OFF);  // [2 pos][384] while Z is idle
         for (int b = 0; b < p.n_blocks; ++b) {
             const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks, ks = p.blk[b].ksize;
             if (b > 0 && p.blk[b].eca_chunk0 >= 0) {
                 // ---- ECA on the block input (builder_util.py:49-80, 481-483), inside the kernel:
-                // gate[o] = hardsigmoid(Wc[o,:] . mean + b[o]) on CUDA cores, Wc tiles [128 rows x
-                // 64 K] arriving through the weight ring; x' = x * gate in place, block m at a time.
+                // gate[o] = hardsigmoid(Wc[o,:] . mean + b[o]).  The matvec runs on the tensor core
+                // (MMA warp: Wc tiles from the weight ring x the fp16 means this block's predecessor
+                // parked in the Z buffer, N = 16 with columns 0/1 = the two positions); here the
+                // pre-activation of this thread's channel comes back from TMEM and scales its X row.
                 const float* eb = p.bias2 + p.blk[b].eca_bias_off;
-                const float* mrow = zmean + h * 384;
 #pragma unroll 1
                 for (int m = 0; m < 3; ++m) {
                     const float ebias = __ldg(eb + m * 128 + r);
-                    float acc = 0.0f;
-#pragma unroll 1
-                    for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
-                        mbar_wait(&bars[TB_PAIR_FULL + b2], gcount & 1);
-#pragma unroll
-                        for (int j = 0; j < 2; ++j) {
-                            const int kb = 2 * b2 + j;
-                            const uint8_t* wrow = smem + TR_RING_OFF + kb * TR_SLOT_BYTES + r * 128;
-#pragma unroll
-                            for (int c = 0; c < 8; ++c) {
-                                const uint4 wv = *reinterpret_cast<const uint4*>(wrow + ((c ^ key) << 4));
-                                const float4 m0 = *reinterpret_cast<const float4*>(mrow + kb * 64 + c * 8);
-                                const float4 m1 = *reinterpret_cast<const float4*>(mrow + kb * 64 + c * 8 + 4);
-                                const float2 w0 = unpack_act2(wv.x), w1 = unpack_act2(wv.y),
-                                             w2 = unpack_act2(wv.z), w3 = unpack_act2(wv.w);
-                                acc = fmaf(w0.x, m0.x, acc); acc = fmaf(w0.y, m0.y, acc);
-                                acc = fmaf(w1.x, m0.z, acc); acc = fmaf(w1.y, m0.w, acc);
-                                acc = fmaf(w2.x, m1.x, acc); acc = fmaf(w2.y, m1.y, acc);
-                                acc = fmaf(w3.x, m1.z, acc); acc = fmaf(w3.y, m1.w, acc);
-                            }
-                        }
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&bars[TB_ECA_DONE + b2]);
-                    }
-                    ++gcount;
+                    { unsigned long long* tr_trace = ctrace; TR_MARK(2, 30); }
+                    tr_wait_full(&bars[TB_ECA_DONE + m], eca_cnt);
+                    tc_fence_after();
+                    { unsigned long long* tr_trace = ctrace; TR_MARK(2, 31 + m); }
+                    uint32_t g0, g1;
+                    tmem_ld_32x32b_x2(tm_d2 + lane_off + m * 16, g0, g1);
+                    tmem_ld_wait();
+                    tc_fence_before();
+                    const float acc = __uint_as_float(h == 0 ? g0 : g1);
                     // torch.nn.Hardsigmoid: relu6(x + 3) / 6
                     const float g = fminf(fmaxf((acc + ebias) * (1.0f / 6.0f) + 0.5f, 0.0f), 1.0f);
                     uint8_t* xrow = smem + TR_X_OFF + m * 32768 + row_off;
@@ -576,9 +576,10 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                     fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&bars[TB_X_READY + m]);
+                    { unsigned long long* tr_trace = ctrace; TR_MARK(2, 35); }
                 }
+                ++eca_cnt;
             }
-            gcount += 2 * nch;
             {
                 const float* par0 = p.par + static_cast<size_t>(g0) * TR_PAR_FLOATS;
                 uint8_t* zrow = smem + TR_Z_OFF + row_off;
@@ -644,10 +645,23 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 { unsigned long long* tr_trace = ctrace; TR_MARK(2, 9); }
             }
             if (want_means) {
-                // every pw2 of this block has completed (D2_FULL[2]), so Z is idle: park the means there
+                // every pw2 of this block has completed (D2_FULL[2]), so Z is idle: park the channel means
+                // there as the K-major fp16 B operand of the ECA matvec: per 64-channel K block 16 rows
+                // of 128 bytes (row 0 / 1 = position 0 / 1, rows 2..15 zero), 128-byte swizzle
+                uint8_t* zm = smem + TR_Z_OFF;
 #pragma unroll
-                for (int m = 0; m < 3; ++m) zmean[h * 384 + m * 128 + r] = sums3[m] * (1.0f / 64.0f);
-                named_bar_sync(2, TR_COMPUTE);
+                for (int m = 0; m < 3; ++m) {
+                    const int ch = m * 128 + r, kb = ch >> 6, k = ch & 63;
+                    *reinterpret_cast<act_t*>(zm + kb * 2048 + h * 128 + (((k >> 3) ^ h) << 4) + (k & 7) * 2) =
+                        float_to_act(sums3[m] * (1.0f / 64.0f));
+                }
+                for (int i = threadIdx.x - 64; i < 6 * 14 * 8; i += TR_COMPUTE) {
+                    const int kb = i / 112, rem = i - kb * 112;
+                    *reinterpret_cast<uint4*>(zm + kb * 2048 + (2 + (rem >> 3)) * 128 + ((rem & 7) << 4)) = make_uint4(0, 0, 0, 0);
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bars[TB_ECA_READY]);
             }
         }
         if (prof != nullptr && lane == 0)   // tail of role 2's region: tag 100 + warp
