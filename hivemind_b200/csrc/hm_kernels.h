@@ -1,4 +1,4 @@
-// hm_kernels.h — launchers of the non-GEMM kernels (planes, ECA gate, value tail,
+// hm_kernels.h — launchers of the non-GEMM kernels (planes, value tail, crossboard token kernels,
 // policy gather/softmax, value shaping).  All take the stream to launch on.
 #pragma once
 #include <cuda_runtime.h>
@@ -17,11 +17,6 @@ constexpr int POLICY_CH = 146;       // two 73-channel projections stacked (boar
 void launch_planes_nchw(const hm_packed_pos* pos, int n, void* out, int dtype, cudaStream_t s);
 
 // ---- stage F, non-GEMM layers ---------------------------------------------------------------
-// ECA gate (builder_util.py:49-80 with hard sigmoid) from per-position channel sums:
-// gate[n][384] = hardsigmoid(Wc * (sums / 64) + b).  wt: [384 in][384 out] 16-bit (centre tap,
-// transposed), b: [384] fp32.
-void launch_eca_gate(const float* sums, const act_t* wt, const float* b, float* gate, int n,
-                     cudaStream_t s);
 // value head tail (builder_util.py:311-324): feat [n,16,64] 16-bit (after conv+BN+ReLU),
 // w4: [1024][4] fp32 (3 wdl rows + plys row of the Linear weights, feature index c*64+sq),
 // b4: [4].  raw5: [n,5] fp32 {value, wdl_loss, wdl_draw, wdl_win, moves_left};

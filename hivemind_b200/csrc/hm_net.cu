@@ -325,12 +325,6 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
                 return nullptr;
             }
             blk.eca = true;
-            std::vector<act_t> wt(384 * 384);
-            for (int o = 0; o < 384; ++o)
-                for (int k = 0; k < 384; ++k) wt[k * 384 + o] = float_to_act(ew->data[o * 384 + k]);
-            blk.eca_wt = upload(*net, wt);
-            blk.eca_b = upload(*net, std::vector<float>(eb->data, eb->data + 384));
-            if (!blk.eca_wt || !blk.eca_b) return nullptr;
             net->param_count += ew->numel() + eb->numel();
             // in-kernel ECA (hm_trunk.cuh): Wc [384 out][384 in] rides in W1cat as 3 extra row
             // chunks (same [rows][384] K-major shape as W1), its bias in the bias2 array
@@ -462,7 +456,7 @@ bool trace_trunk_run(Worker& w, int run, unsigned long long* out_host, int* cap)
 
 // A run of consecutive bottleneck blocks [first, last) as one trunk_kernel launch.
 static bool add_trunk_run(Worker& w, std::vector<Op>& ops, const Net& net, int first, int last, act_t* x,
-                          const float* gate, float* sums, int n_pos) {
+                          int n_pos) {
     if (last - first > TR_MAX_BLOCKS) { set_error("trunk run too long"); return false; }
     CUtensorMap tm_x;
     if (!make_tm_act3(&tm_x, x, n_pos, 384)) return false;
@@ -477,8 +471,6 @@ static bool add_trunk_run(Worker& w, std::vector<Op>& ops, const Net& net, int f
     }
     p.par = net.trunk_par;
     p.bias2 = net.trunk_bias2;
-    p.gate = gate;
-    p.sums = sums;
     p.trace = nullptr;
     p.dbg = 0;
     if (const char* dbg = getenv("HM_TRUNK_DBG")) p.dbg = atoi(dbg);  // timing experiments only (wrong results)
@@ -657,7 +649,6 @@ static bool setup_worker(Engine* e, Worker& w) {
               dev_alloc(w, &w.d_trunk, nb * 384 * 64) && dev_alloc(w, &w.d_pol_shared, nb * 384 * 64) &&
               dev_alloc(w, &w.d_logits, nb * POLICY_CH * 64) && dev_alloc(w, &w.d_pi, nb * POLICY_CH * 64) &&
               dev_alloc(w, &w.d_vfeat, nb * 16 * 64) && dev_alloc(w, &w.d_raw5, nb * 5) &&
-              dev_alloc(w, &w.d_sums, nb * 384) && dev_alloc(w, &w.d_gate, nb * 384) &&
               dev_alloc(w, &w.d_value_h, nb) && dev_alloc(w, &w.d_wdl_h, nb * 3) && dev_alloc(w, &w.d_ml_h, nb);
     ok = ok && host_alloc(w, &w.h_pos, nb) && host_alloc(w, &w.h_moves, w.move_cap) &&
          host_alloc(w, &w.h_offsets, 2 * nb + 1) && host_alloc(w, &w.h_priors, w.move_cap) &&
@@ -673,32 +664,11 @@ static bool setup_worker(Engine* e, Worker& w) {
     int nblk = static_cast<int>(net.blocks.size());
     if (const char* stop = getenv("HM_TRUNK_STOP"))  // debugging aid (tools/diagnose.py): truncate the trunk
         nblk = std::max(0, std::min(nblk, atoi(stop)));
-    // the whole trunk is one launch: ECA gates inside a run are computed in the kernel (a gate
-    // depends on the channel means of the SAME position only, builder_util.py:77-80); a run
-    // longer than TR_MAX_BLOCKS would be cut, with the gate of its first block from eca_gate_kernel
-    for (int first = 0; first < nblk;) {
-        int last = first + 1;
-        while (last < nblk && last - first < TR_MAX_BLOCKS) ++last;
-        const Block& b0 = net.blocks[first];
-        const float* gate = nullptr;
-        if (b0.eca) {
-            if (first == 0) { set_error("ECA on the first block is not supported"); return false; }
-            Op op;
-            op.name = "b" + std::to_string(first) + ".eca_gate";
-            op.klass = "eca";
-            op.bytes = static_cast<double>(B) * 384 * 8;
-            const float* sums = w.d_sums;
-            const act_t* wt = b0.eca_wt;
-            const float* eb = b0.eca_b;
-            float* g = w.d_gate;
-            op.launch = [sums, wt, eb, g, B](cudaStream_t s) { launch_eca_gate(sums, wt, eb, g, B, s); };
-            ops.push_back(std::move(op));
-            gate = w.d_gate;
-        }
-        float* sums = (last < nblk && net.blocks[last].eca) ? w.d_sums : nullptr;
-        if (!add_trunk_run(w, ops, net, first, last, w.d_trunk, gate, sums, B)) return false;
-        first = last;
-    }
+    // the whole trunk is ONE launch: ECA gates are computed inside the kernel (a gate depends on the
+    // channel means of the SAME position only, builder_util.py:77-80)
+    if (nblk > TR_MAX_BLOCKS) { set_error("trunks longer than TR_MAX_BLOCKS blocks are not supported"); return false; }
+    if (nblk > 0 && net.blocks[0].eca) { set_error("ECA on the first block is not supported"); return false; }
+    if (nblk > 0 && !add_trunk_run(w, ops, net, 0, nblk, w.d_trunk, B)) return false;
     w.debug_views["planes"] = {w.d_planes, {B, HM_NB_INPUT_VALUES, 0}};
     w.debug_views["trunk"] = {w.d_trunk, {B, 384 * 64, 0}};
     const bool cross = net.arch == HM_ARCH_CROSSBOARD_RISEV33;

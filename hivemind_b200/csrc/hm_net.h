@@ -55,8 +55,6 @@ struct Block {                 // one bottleneck block inside the trunk kernel (
     int bias2_off = 0;             // offset into Net::trunk_bias2
     int eca_chunk0 = -1;           // row chunk of the ECA weight inside W1cat (in-kernel ECA)
     int eca_bias_off = 0;          // offset of the ECA bias inside Net::trunk_bias2
-    act_t* eca_wt = nullptr;       // [384 in][384 out]
-    float* eca_b = nullptr;
     double macs_per_pos() const { return 2.0 * 64.0 * 384.0 * cop; }
 };
 struct XLayer {                // one _CrossBoardAttentionBlock (rise_mobile_v3.py:242-278)
@@ -127,8 +125,6 @@ struct Worker {
     __half* d_pi = nullptr;         // [B][146][64] fp16 (reference-shaped path): A = ch 0..72, B = 73..145
     act_t* d_vfeat = nullptr;       // [B][16][64]
     float* d_raw5 = nullptr;
-    float* d_sums = nullptr;        // [B][384] channel sums for the next ECA gate
-    float* d_gate = nullptr;        // [B][384]
     __half *d_value_h = nullptr, *d_wdl_h = nullptr, *d_ml_h = nullptr;
     // crossboard-risev33 (arch 1): tokens [B][2][192][64] channel-major and their intermediates
     float* d_tokpre = nullptr;      // fp32 [B][384][64]

@@ -44,12 +44,11 @@ struct TrunkParams {
     TrunkBlock blk[TR_MAX_BLOCKS];
     const float* par;    // [chunk][TR_PAR_FLOATS]
     const float* bias2;  // [...][384]
-    const float* gate;   // [pos][384] ECA gate of the run's first block, or nullptr
-    float* sums;         // [pos][384] channel sums (over 64 squares) of the run's output, or nullptr
     unsigned long long* trace;  // bring-up aid: CTA 0 logs (tag << 48 | clock) per role, or nullptr
     int dbg;                    // bring-up aid (timing experiments only, results are wrong when set):
-                                // bit0 skip depthwise math, bit1 skip TMEM drain, bit2 skip Z store,
-                                // bit3 / bit4 skip the math only on sub-partitions 0,1 / 2,3
+                                // 1 skip depthwise math, 2 skip TMEM drain, 4 skip Z store, 8 / 16 skip the
+                                // math only on sub-partitions 0,1 / 2,3, 64 scalar-FFMA depthwise (results
+                                // stay right), 128 weight ring + MMAs only (compute warps idle)
 };
 
 // timeline tracing (tools/trace_trunk.py): roles 0 = producer, 1 = MMA issuer, 2 = compute warp 2
@@ -232,19 +231,6 @@ __device__ __forceinline__ void trunk_chunk(ChunkPar<KS>& cur, const float* __re
     if ((dbg & 1) || ((dbg & 8) && ((threadIdx.x >> 5) & 3) < 2) || ((dbg & 16) && ((threadIdx.x >> 5) & 3) >= 2)) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) packed[j] = __float_as_uint(y[2 * j]);
-    } else if (dbg & 32) {
-        // experiment: the same number of FFMAs as the depthwise from a ROLLED loop (tiny code
-        // footprint) -> separates issue-slot pressure from instruction-cache pressure
-        float a[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) a[j] = y[j];
-#pragma unroll 1
-        for (int it = 0; it < (KS == 3 ? 60 : 144); ++it) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) a[j] = fmaf(a[j], cur.w[j], y[8 + j]);
-        }
-#pragma unroll
-        for (int j = 0; j < 32; ++j) packed[j] = __float_as_uint(a[j & 7] + y[2 * j]);
     } else {
         const long long t0 = prof ? clock64() : 0;
         if (dbg & 64) dw_board<KS>(y, cur.w, cur.bd, packed);   // scalar FFMA variant kept for A/B timing
@@ -500,33 +486,11 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         const int h = (warp - 2) >> 2;      // position of the tile handled by this warp
         const int r = q * 32 + lane;        // channel within a 128-channel chunk / M block
         const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
-        const int pos = tile * 2 + h;
         const int key = r & 7;
         // this thread's 128-byte row inside a [2 pos][64 ch][64 sq] block
         const uint32_t row_off = (r >> 6) * 16384 + h * 8192 + (r & 63) * 128;
 
-        // ---- segment input: optional ECA gate (builder_util.py:77-80, 481-483), x' = x * gate ----
-        tr_wait_full(&bars[TB_X_FULL], 0);
-        if (p.gate != nullptr) {
-#pragma unroll
-            for (int m = 0; m < 3; ++m) {
-                const float g = __ldg(p.gate + static_cast<size_t>(pos) * 384 + m * 128 + r);
-                uint8_t* xrow = smem + TR_X_OFF + m * 32768 + row_off;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    uint4* px = reinterpret_cast<uint4*>(xrow + ((j ^ key) << 4));
-                    uint4 v = *px;
-                    float2 a = unpack_act2(v.x), b = unpack_act2(v.y), c = unpack_act2(v.z), d = unpack_act2(v.w);
-                    v.x = pack_act2(a.x * g, a.y * g);
-                    v.y = pack_act2(b.x * g, b.y * g);
-                    v.z = pack_act2(c.x * g, c.y * g);
-                    v.w = pack_act2(d.x * g, d.y * g);
-                    *px = v;
-                }
-            }
-            fence_proxy_async_smem();
-        }
-        __syncwarp();
+        tr_wait_full(&bars[TB_X_FULL], 0);   // the tile's block input has landed
         if (lane == 0) {
             mbar_arrive(&bars[TB_X_READY + 0]);
             mbar_arrive(&bars[TB_X_READY + 1]);
@@ -592,7 +556,6 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             const bool last = (b + 1 == p.n_blocks);
             const float* b2 = p.bias2 + p.blk[b].bias2_off;
             const bool want_means = !last && p.blk[b + 1].eca_chunk0 >= 0;  // next block gates its input
-            const bool want_sums = (last && p.sums != nullptr) || want_means;
             float sums3[3];
 #pragma unroll
             for (int m = 0; m < 3; ++m) {
@@ -622,7 +585,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                         const float2 acc = __fadd2_rn(make_float2(__uint_as_float(a[i]), __uint_as_float(a[i + 1])), bb);
                         const float2 o = __fadd2_rn(acc, unpack_act2(ru[e]));
                         ou[e] = pack_act2(o.x, o.y);
-                        if (want_sums) {  // ECA squeeze of the next run: sum of what was actually stored
+                        if (want_means) {  // ECA squeeze of the next block: sum of what was actually stored
                             const float2 rd = unpack_act2(ou[e]);
                             s += rd.x;
                             s1 += rd.y;
@@ -637,7 +600,6 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 for (int j = 4; j < 8; ++j) piece(j, a1, 32);
                 s += s1;
                 sums3[m] = s;
-                if (last && p.sums != nullptr) p.sums[static_cast<size_t>(pos) * 384 + m * 128 + r] = s;
                 tc_fence_before();
                 fence_proxy_async_smem();
                 __syncwarp();
