@@ -40,6 +40,7 @@ struct CgemmParams {
     int relu;           // activation: 0 none, 1 ReLU, 2 GELU (erf form, nn.GELU default)
     int out_f32;
     const act_t* residual;  // optional [pos][out_channels][64], added before the activation
+    int ksteps_last;    // valid 16-channel K steps (1..8) in the last 128-channel K pair: the rest is zero padding
     int stages;         // ring depth (1..CG_STAGES); shallow-K 1x1 layers use 1 so that 3 CTAs share an SM
 };
 
@@ -115,12 +116,14 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
         for (int ky = 0; ky < p.ksize; ++ky) {
             const int sq0 = 8 * (ky - (p.ksize >> 1));   // vertical tap offset as a square shift
             for (int kp = 0; kp < kpairs; ++kp) {
+                // the upper 64 channels of the last pair may be pure padding: neither loaded nor multiplied
+                const bool upper = kp + 1 < kpairs || p.ksteps_last > 4;
                 mbar_wait(&empty_x[xs], xphase);
                 if (leader) {
                     uint8_t* dst = smem_x + xs * CG_STAGE_BYTES;
-                    mbar_arrive_expect_tx(&full_x[xs], CG_STAGE_BYTES);
+                    mbar_arrive_expect_tx(&full_x[xs], upper ? CG_STAGE_BYTES : CG_STAGE_BYTES / 2);
                     tma_load_3d(dst, &tmX, &full_x[xs], sq0, kp * 128, pos0);
-                    tma_load_3d(dst + 16384, &tmX, &full_x[xs], sq0, kp * 128 + 64, pos0);
+                    if (upper) tma_load_3d(dst + 16384, &tmX, &full_x[xs], sq0, kp * 128 + 64, pos0);
                 }
                 __syncwarp();
                 if (++xs == n_x) { xs = 0; xphase ^= 1; }
@@ -129,9 +132,9 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
                     mbar_wait(&empty_w[ws], wphase);
                     if (leader) {
                         uint8_t* dst = smem + ws * CG_STAGE_BYTES;
-                        mbar_arrive_expect_tx(&full_w[ws], CG_STAGE_BYTES);
+                        mbar_arrive_expect_tx(&full_w[ws], upper ? CG_STAGE_BYTES : CG_STAGE_BYTES / 2);
                         tma_load_2d(dst, &tmW, &full_w[ws], kcol, row0);
-                        tma_load_2d(dst + 16384, &tmW, &full_w[ws], kcol + 64, row0);
+                        if (upper) tma_load_2d(dst + 16384, &tmW, &full_w[ws], kcol + 64, row0);
                     }
                     __syncwarp();
                     if (++ws == n_w) { ws = 0; wphase ^= 1; }
@@ -149,6 +152,7 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
             for (int kp = 0; kp < kpairs; ++kp) {
                 mbar_wait(&full_x[xs], xphase);
                 const uint32_t xo = xs * (CG_STAGE_BYTES / 16);
+                const int nk = kp + 1 < kpairs ? 8 : p.ksteps_last;   // K steps that hold real channels
                 for (int kx = 0; kx < p.ksize; ++kx) {       // accumulator = horizontal offset kx
                     const uint32_t d = tmem_base + kx * 128;
                     mbar_wait(&full_w[ws], wphase);
@@ -160,8 +164,9 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
                         for (int j = 0; j < 2; ++j) {
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
-                                umma_f16(d, a0 + (wo + j * 1024 + 2 * k), b0 + (xo + j * 1024 + k * 128), idesc,
-                                         (j | k) ? 1u : acc0);
+                                if (j * 4 + k < nk)
+                                    umma_f16(d, a0 + (wo + j * 1024 + 2 * k), b0 + (xo + j * 1024 + k * 128), idesc,
+                                             (j | k) ? 1u : acc0);
                         }
                         umma_commit(&empty_w[ws]);
                         if (kx == p.ksize - 1) umma_commit(&empty_x[xs]);

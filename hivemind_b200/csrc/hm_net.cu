@@ -510,6 +510,10 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
     p.n_valid = L.cout;
     p.ksize = L.ksize;
     p.kblocks = L.cpad / 64;
+    {
+        const int rem = L.cin - (L.cpad / 128 - 1) * 128;   // real channels in the last 128-channel K pair
+        p.ksteps_last = std::max(1, std::min(8, (rem + 15) / 16));
+    }
     p.bias = L.bias;
     p.out = io.out;
     p.out_channels = io.out_channels ? io.out_channels : L.cout;
@@ -625,12 +629,29 @@ static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int 
     return true;
 }
 
+// The value head (value.* ops: fusion/conv/tail/shape) only reads the trunk (or token) output, so
+// it is captured as a parallel graph branch beside the policy head: the fork is placed before the
+// first value op, the join after the last op of the lists.
 static bool capture_graph(Worker& w, const std::vector<const std::vector<Op>*>& lists,
                           cudaGraphExec_t* exec) {
     cudaGraph_t graph = nullptr;
+    const bool branch = getenv("HM_NO_GRAPH_BRANCH") == nullptr;
     if (!cuda_ok(cudaStreamBeginCapture(w.stream, cudaStreamCaptureModeThreadLocal), "BeginCapture")) return false;
+    bool forked = false;
     for (auto* l : lists)
-        for (const Op& op : *l) op.launch(w.stream);
+        for (const Op& op : *l) {
+            const bool side = branch && op.name.rfind("value.", 0) == 0;
+            if (side && !forked) {
+                cudaEventRecord(w.ev_fork, w.stream);
+                cudaStreamWaitEvent(w.side_stream, w.ev_fork, 0);
+                forked = true;
+            }
+            op.launch(side ? w.side_stream : w.stream);
+        }
+    if (forked) {
+        cudaEventRecord(w.ev_join, w.side_stream);
+        cudaStreamWaitEvent(w.stream, w.ev_join, 0);
+    }
     if (!cuda_ok(cudaStreamEndCapture(w.stream, &graph), "EndCapture")) return false;
     const bool ok = cuda_ok(cudaGraphInstantiate(exec, graph, 0), "GraphInstantiate");
     cudaGraphDestroy(graph);
@@ -643,6 +664,9 @@ static bool setup_worker(Engine* e, Worker& w) {
     const size_t nb = static_cast<size_t>(B);
     w.move_cap = nb * 2 * 256;
     if (!cuda_ok(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
+    if (!cuda_ok(cudaStreamCreateWithFlags(&w.side_stream, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
+    if (!cuda_ok(cudaEventCreateWithFlags(&w.ev_fork, cudaEventDisableTiming), "cudaEventCreate") ||
+        !cuda_ok(cudaEventCreateWithFlags(&w.ev_join, cudaEventDisableTiming), "cudaEventCreate")) return false;
     bool ok = dev_alloc(w, &w.d_pos, nb) && dev_alloc(w, &w.d_moves, w.move_cap) &&
               dev_alloc(w, &w.d_offsets, 2 * nb + 1) && dev_alloc(w, &w.d_priors, w.move_cap) &&
               dev_alloc(w, &w.d_values, nb) && dev_alloc(w, &w.d_planes, nb * HM_NB_INPUT_VALUES) &&
@@ -671,6 +695,10 @@ static bool setup_worker(Engine* e, Worker& w) {
     if (nblk > 0 && !add_trunk_run(w, ops, net, 0, nblk, w.d_trunk, B)) return false;
     w.debug_views["planes"] = {w.d_planes, {B, HM_NB_INPUT_VALUES, 0}};
     w.debug_views["trunk"] = {w.d_trunk, {B, 384 * 64, 0}};
+    {
+        void* clk = nullptr;
+        if (cudaGetSymbolAddress(&clk, g_trunk_clk) == cudaSuccess) w.debug_views["trunk_clk"] = {clk, {1, 16, 1}};
+    }
     const bool cross = net.arch == HM_ARCH_CROSSBOARD_RISEV33;
     act_t* tokens = nullptr;
     if (cross && !add_crossboard(w, ops, net, B, &tokens)) return false;
@@ -783,6 +811,9 @@ void engine_free_workers(Engine* e) {
         for (void* p : w->dev_allocs) cudaFree(p);
         for (void* p : w->host_allocs) cudaFreeHost(p);
         if (w->stream) cudaStreamDestroy(w->stream);
+        if (w->side_stream) cudaStreamDestroy(w->side_stream);
+        if (w->ev_fork) cudaEventDestroy(w->ev_fork);
+        if (w->ev_join) cudaEventDestroy(w->ev_join);
     }
     e->workers.clear();
 }

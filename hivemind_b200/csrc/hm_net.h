@@ -108,6 +108,8 @@ struct Worker {
     int batch = 0;        // positions per request (even)
     size_t move_cap = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t side_stream = nullptr;   // captured only: the value-head branch of the graphs
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool pending = false;
     int pending_kind = 0;  // 1 = dense half request, 2 = packed positions request
     size_t pending_npos = 0, pending_nmoves = 0;

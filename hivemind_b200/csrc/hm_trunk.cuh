@@ -271,6 +271,15 @@ __device__ __forceinline__ void trunk_block_chunks(const float* __restrict__ par
     }
 }
 
+// effective-clock probe: CTA 0 and the last CTA record (SM cycles, nanoseconds) of their lifetime
+// (debug view "trunk_clk"; tools/trunk_clock.py)
+__device__ float g_trunk_clk[16];   // [0..3] lifetimes; [4..] CTA 0 phase marks (cycles since kernel entry)
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 __global__ void __launch_bounds__(TR_THREADS, 1)
 trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUtensorMap tmX,
              const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2) {
@@ -283,6 +292,11 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x;
     unsigned long long* const tr_trace = (blockIdx.x == 0 && (lane == 0)) ? p.trace : nullptr;
+    const long long clk_base = clock64();
+#define TR_CLK(i) do { if (blockIdx.x == 0 && lane == 0) g_trunk_clk[4 + (i)] = static_cast<float>(clock64() - clk_base); } while (0)
+    const bool clk_probe = threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1);
+    const long long clk_c0 = clk_probe ? clock64() : 0;
+    const unsigned long long clk_t0 = clk_probe ? global_timer_ns() : 0;
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmX);
@@ -304,6 +318,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (warp == 0) TR_CLK(0);   // prologue done
     const uint32_t tm_d2 = tmem_base;
     const uint32_t tm_d1 = tmem_base + 384u;
 
@@ -360,7 +375,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             }
             par ^= 1;
         };
-        for (int b = 0; b < p.n_blocks; ++b) {
+        for (int b = 0; b < ((p.dbg & 256) ? 0 : p.n_blocks); ++b) {
             const int g0 = p.blk[b].chunk0, nch = p.blk[b].n_chunks;
             if (b > 0 && p.blk[b].eca_chunk0 >= 0)   // in-kernel ECA: Wc streams through the ring like W1
                 for (int m = 0; m < 3; ++m) group_w1(p.blk[b].eca_chunk0 + m);
@@ -393,7 +408,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
 #pragma unroll
             for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
                 if (xblock >= 0) tr_wait_full(&bars[TB_X_READY + b2], xblock);  // X blocks 2*b2, 2*b2+1 ready
-                mbar_wait(&bars[TB_PAIR_FULL + b2], par);
+                if (!(p.dbg & 256)) mbar_wait(&bars[TB_PAIR_FULL + b2], par);
                 tc_fence_after();
                 TR_MARK(1, 10 + b2);
                 if (leader) {
@@ -415,7 +430,9 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             TR_MARK(1, 3);
         };
         uint32_t eca_n = 0;
+        TR_CLK(1);   // issuer enters its loop
         for (int b = 0; b < p.n_blocks; ++b) {
+            if (b == 1) TR_CLK(6);   // block 0 issued
             const int nch = p.blk[b].n_chunks;
             if (b > 0 && p.blk[b].eca_chunk0 >= 0) {
                 // ECA matvec on the tensor core: G[m] (128 out channels x N = 16, columns 0/1 = the
@@ -427,7 +444,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 for (int m = 0; m < 3; ++m) {
 #pragma unroll
                     for (int b2 = 0; b2 < TR_PAIRS; ++b2) {
-                        mbar_wait(&bars[TB_PAIR_FULL + b2], par);
+                        if (!(p.dbg & 256)) mbar_wait(&bars[TB_PAIR_FULL + b2], par);
                         tc_fence_after();
                         if (leader) {
 #pragma unroll
@@ -458,7 +475,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 const bool last_chunk = c + 1 == nch;
 #pragma unroll
                 for (int m = 0; m < TR_PAIRS; ++m) {   // pair = output channel block m
-                    mbar_wait(&bars[TB_PAIR_FULL + m], par);
+                    if (!(p.dbg & 256)) mbar_wait(&bars[TB_PAIR_FULL + m], par);
                     tc_fence_after();
                     TR_MARK(1, 20 + m);
                     if (leader) {
@@ -480,6 +497,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 TR_MARK(1, 6);
             }
         }
+        TR_CLK(2);   // last MMA issued
     } else {
         // ================================ compute warps ================================
         const int q = warp & 3;             // TMEM lane quarter this warp may access
@@ -491,6 +509,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         const uint32_t row_off = (r >> 6) * 16384 + h * 8192 + (r & 63) * 128;
 
         tr_wait_full(&bars[TB_X_FULL], 0);   // the tile's block input has landed
+        if (warp == 2) TR_CLK(5);   // X landed
         if (lane == 0) {
             mbar_arrive(&bars[TB_X_READY + 0]);
             mbar_arrive(&bars[TB_X_READY + 1]);
@@ -630,11 +649,13 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
             p.trace[3 * TR_TRACE_CAP - 16 + warp] =
                 (static_cast<unsigned long long>(100 + warp) << 48) | (static_cast<unsigned long long>(math_cycles) & 0xffffffffffffull);
         // ---- run output: shared-memory tile -> global (TMA store) ----
+        if (warp == 2) TR_CLK(3);   // last block epilogue done
         named_bar_sync(1, TR_COMPUTE);
         if (threadIdx.x == 64) {
             for (int kb = 0; kb < 6; ++kb) tma_store_3d(&tmX, smem + TR_X_OFF + kb * 16384, 0, kb * 64, tile * 2);
             bulk_commit_group();
             bulk_wait_group0();
+            TR_CLK(4);   // output stored
         }
     }
     tc_fence_before();
@@ -642,6 +663,11 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
+    }
+    if (clk_probe) {
+        const int o = blockIdx.x == 0 ? 0 : 2;
+        g_trunk_clk[o] = static_cast<float>(clock64() - clk_c0);
+        g_trunk_clk[o + 1] = static_cast<float>(global_timer_ns() - clk_t0);
     }
 }
 

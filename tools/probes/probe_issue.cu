@@ -1,0 +1,177 @@
+// Probe: what bounds a single-thread tcgen05.mma issue loop that re-uses smem slots?  probe_mcast.cu showed
+// the weight ring runs at the same 270.6 (8 MMAs per barrier) / 328 (4 per barrier) cycles per 16 KB tile
+// with or without TMA traffic, i.e. the limit is the issuing thread, not L2->SM bandwidth.  Here the MMA
+// thread runs alone on fixed operands:
+//   MODE 0  MMAs only                      MODE 1  + commit per group
+//   MODE 2  + mbarrier wait before a group (the barrier was completed NB groups ago)
+//   MODE 4  as 2, but the try_wait for the NEXT group is issued before this group's MMAs and its
+//           predicate is consumed after them (software-pipelined wait)
+// NDIM < 128 shortens the tensor time per MMA (N/2 cycles) and exposes the thread's issue cost.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -o probe_issue probe_issue.cu
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cstdio>
+#include <cstdlib>
+#include "../../hivemind_b200/csrc/hm_ptx.cuh"
+using namespace hm;
+
+// one tile = 4 MMAs (K = 64) + commit to `bar`; starts a try_wait on `next_bar` first, returns its outcome
+__device__ __forceinline__ uint32_t tile_deferred(uint32_t tmem, uint32_t a_lo, uint32_t a_hi, const uint32_t (&b_lo)[4],
+                                                  uint32_t b_hi, uint32_t idesc, uint64_t* bar, uint64_t* next_bar,
+                                                  uint32_t next_par) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t.reg .b32 t;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 q, [%10], %11;\n\t"
+        "setp.ne.b32 p, %8, 0;\n\t"
+        "mov.b64 da, {%2, %3};\n\t mov.b64 db, {%4, %12};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%1], da, db, %8, p;\n\t"
+        "add.u32 t, %2, 2;\n\t mov.b64 da, {t, %3};\n\t mov.b64 db, {%5, %12};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%1], da, db, %8, p;\n\t"
+        "add.u32 t, %2, 4;\n\t mov.b64 da, {t, %3};\n\t mov.b64 db, {%6, %12};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%1], da, db, %8, p;\n\t"
+        "add.u32 t, %2, 6;\n\t mov.b64 da, {t, %3};\n\t mov.b64 db, {%7, %12};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%1], da, db, %8, p;\n\t"
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%9];\n\t"
+        "selp.u32 %0, 1, 0, q;\n\t}"
+        : "=r"(ok)
+        : "r"(tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo[0]), "r"(b_lo[1]), "r"(b_lo[2]), "r"(b_lo[3]), "r"(idesc),
+          "r"(smem_u32(bar)), "r"(smem_u32(next_bar)), "r"(next_par), "r"(b_hi)
+        : "memory");
+    return ok;
+}
+
+template <int GROUP, int NB, int MODE, int NDIM, bool ELECT>
+__global__ void __launch_bounds__(352, 1) mmaonly(int n_groups, long long* cycles_out, int spin) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* bop = smem;
+    uint8_t* ringp = smem + 16384;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(ringp + NB * GROUP * 16384);
+    uint32_t* slot = reinterpret_cast<uint32_t*>(bars + 32);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 32; ++i) mbar_init(&bars[i], 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) { tmem_alloc(slot, 128); tmem_relinquish(); }
+    for (int i = threadIdx.x; i < 4096 * (1 + NB * GROUP); i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *slot;
+    if (warp == 1 && (ELECT || lane == 0)) {
+        const bool leader = ELECT ? elect_one() : true;
+        const uint32_t idesc = umma_idesc_16_bmn(128, NDIM, 0);
+        const uint64_t a0 = umma_desc_sw128(smem_u32(ringp));
+        const uint32_t a_lo = static_cast<uint32_t>(a0), a_hi = static_cast<uint32_t>(a0 >> 32);
+        uint64_t bd[4];
+        uint32_t b_lo[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { bd[k] = umma_desc_mn_sw128(smem_u32(bop) + k * 2048, 8192, 1024); b_lo[k] = static_cast<uint32_t>(bd[k]); }
+        const uint32_t b_hi = static_cast<uint32_t>(bd[0] >> 32);
+        long long t0 = clock64();
+        uint32_t par = 1;
+        if (MODE == 4) {
+            // invariant: the barrier of the group about to be issued is known complete
+            mbar_wait(&bars[0], par);
+            for (int g = 0; g < n_groups; g += NB) {
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    uint64_t* nb_bar = &bars[b + 1 == NB ? 0 : b + 1];
+                    const uint32_t npar = b + 1 == NB ? par ^ 1 : par;
+                    uint32_t ok = 1;
+#pragma unroll
+                    for (int j = 0; j < GROUP; ++j) {
+                        // only the last tile of the group commits to the group barrier; earlier ones to a dummy
+                        const uint32_t o = tile_deferred(tmem, a_lo + (b * GROUP + j) * 1024, a_hi, b_lo, b_hi, idesc,
+                                                         j == GROUP - 1 ? &bars[b] : &bars[30], nb_bar, npar);
+                        if (j == GROUP - 1) ok = o;
+                    }
+                    if (!ok) mbar_wait(nb_bar, npar);
+                }
+                par ^= 1;
+            }
+        } else {
+            for (int g = 0; g < n_groups; g += NB) {
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    if (MODE >= 2) mbar_wait(&bars[b], par);
+                    if (leader) {
+#pragma unroll
+                        for (int j = 0; j < GROUP; ++j)
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                umma_f16_lh(tmem, a_lo + (b * GROUP + j) * 1024 + 2 * k, a_hi, b_lo[k], b_hi, idesc, 1u);
+                        if (MODE >= 1) umma_commit(&bars[b]);
+                    }
+                    if (ELECT) __syncwarp();
+                }
+                par ^= 1;
+            }
+        }
+        if (leader) umma_commit(&bars[31]);
+        mbar_wait(&bars[31], 0);
+        cycles_out[0] = clock64() - t0;
+        if (leader) mbar_arrive(&bars[29]);
+    } else if (warp >= 2 && spin) {
+        // bystanders: spin on a barrier that completes only when the MMA thread is done (what the
+        // compute / producer warps of a real kernel do while they wait)
+        if (spin == 1) mbar_wait(&bars[29], 0);
+        else if (spin == 2) { if (lane == 0) mbar_wait(&bars[29], 0); }
+        else {
+            // spin 3: fence.proxy.async every ~period cycles; 4: + tcgen05.ld of the accumulator; 5: STS traffic
+            const int period = 3000;
+            uint32_t sink = 0;
+            while (!mbar_try_wait(&bars[29], 0)) {
+                if (spin == 3) fence_proxy_async_smem();
+                if (spin == 4 && warp < 6) {
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16), r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) sink ^= r[i];
+                }
+                if (spin == 5) {
+                    // 8 KB of 16-byte stores per warp into the (unused) tail of the B block region
+                    for (int i = 0; i < 16; ++i)
+                        reinterpret_cast<uint4*>(smem + 16384 * (1 + NB * GROUP) - 32768)[((warp - 2) * 16 + i) * 32 + lane] = make_uint4(sink, 1, 2, 3);
+                }
+                if (spin == 6) tc_fence_before();
+                if (spin == 7) { tc_fence_before(); fence_proxy_async_smem(); mbar_arrive(&bars[28]); }
+                const long long t1 = clock64() + period;
+                while (clock64() < t1) {}
+            }
+            if (sink == 0x12345678) cycles_out[1] = sink;
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 128); }
+}
+
+template <int GROUP, int NB, int MODE, int NDIM = 128, bool ELECT = true>
+static void run_only(long long* dc, int spin = 0, int threads = 128) {
+    auto kern = mmaonly<GROUP, NB, MODE, NDIM, ELECT>;
+    const int smem = (NB * GROUP + 1) * 16384 + 1024;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const int n_groups = (2400 / (GROUP * NB)) * NB;
+    for (int rep = 0; rep < 2; ++rep) {
+        kern<<<1, threads, smem>>>(n_groups, dc, spin);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("err %s\n", cudaGetErrorString(e)); exit(1); }
+    }
+    long long c;
+    cudaMemcpy(&c, dc, 8, cudaMemcpyDeviceToHost);
+    printf("spin=%d threads=%d %s N=%3d group=%d nb=%2d mode=%d  cycles per 4-MMA tile %8.1f  (tensor floor %d; per group %8.1f)\n", spin, threads, ELECT ? "elect " : "lane0 ", NDIM, GROUP, NB, MODE,
+           (double)c / (n_groups * GROUP), NDIM * 2, (double)c / n_groups);
+}
+
+int main() {
+    long long* dc;
+    cudaMalloc(&dc, 1024 * 8);
+    run_only<2, 3, 2>(dc, 0, 128);
+    for (int sp = 3; sp <= 7; ++sp) run_only<2, 3, 2>(dc, sp, 352);
+    return 0;
+}
