@@ -49,9 +49,9 @@ constexpr int CG_THREADS = 192;
 // channels) and a ring of ACTIVATION stages (two 16 KB B blocks = 128 channels x 2 positions).
 // For a 3x3 convolution one activation stage serves the three horizontal taps kx (they differ
 // only in the weights and in the accumulator, the horizontal shift happens in the epilogue), so
-// the activation tile crosses L2->SM once per (ky, 128 channels) instead of three times: the
-// per-SM L2 ingest (~52-62 B/clk measured, tools/probes/probe_mmaring.cu) is what bounds these
-// layers, not the tensor pipe.  8 MMAs (512 tensor-pipe cycles) per weight-barrier round trip.
+// the activation tile crosses L2->SM once per (ky, 128 channels) instead of three times.
+// 8 MMAs (512 tensor-pipe cycles) per weight-barrier round trip: one thread issues a 16 KB
+// UTMALDG in ~200 cycles and pays ~100 per barrier round (tools/probes/probe_mcast.cu).
 constexpr int CG_WSTAGES = 4;
 constexpr int CG_XSTAGES = 2;
 constexpr int CG_STAGE_BYTES = 32768;

@@ -64,9 +64,10 @@ constexpr int TR_THREADS = 320;
 constexpr int TR_COMPUTE = 256;
 // Weight ring: 6 slots of 16 KB = exactly one "group" (the 6 W1 tiles of a chunk's pw1, or the 6
 // W2 tiles of its pw2), so slot indices are compile-time inside the fully unrolled group loops and
-// the barrier parity simply toggles per group.  One full/empty barrier pair guards TWO slots
-// (32 KB, 8 MMAs): the single-thread producer / issuer loops pay ~100 cycles per barrier round
-// trip, which a 4-MMA (256-cycle) stage cannot hide (tools/probes/probe_mmaring.cu).
+// the barrier parity simply toggles per group.  One "full" barrier guards TWO slots (32 KB,
+// 8 MMAs), "empty" barriers are per slot: a thread pays ~40 cycles per MMA issue or successful
+// wait, ~200 per 16 KB TMA issue and ~100 per barrier round trip (tools/probes/probe_issue.cu,
+// probe_mcast.cu), so both single-thread roles keep up with the 256-cycle tile.
 constexpr int TR_SLOTS = 6;
 constexpr int TR_PAIRS = 3;
 constexpr int TR_SLOT_BYTES = 16384;
