@@ -10,6 +10,7 @@
 #include <mutex>
 
 #include "hm_cgemm.cuh"
+#include "hm_pgemm.cuh"
 #include "hm_trunk.cuh"
 #include "hm_kernels.h"
 
@@ -87,10 +88,10 @@ bool tensormap_init() {
     return g_encode != nullptr;
 }
 // W: 16-bit [rows][kcols] K-major, box = 64 K-elements x 128 rows, 128-byte swizzle.
-static bool make_tm_weights(CUtensorMap* tm, const void* w, size_t rows, int kcols) {
+static bool make_tm_weights(CUtensorMap* tm, const void* w, size_t rows, int kcols, int box_rows = 128) {
     cuuint64_t dims[2] = {static_cast<cuuint64_t>(kcols), static_cast<cuuint64_t>(rows)};
     cuuint64_t strides[1] = {static_cast<cuuint64_t>(kcols) * 2};
-    cuuint32_t box[2] = {64, 128};
+    cuuint32_t box[2] = {64, static_cast<cuuint32_t>(box_rows)};
     cuuint32_t es[2] = {1, 1};
     CUresult r = g_encode(tm, HM_TMA_DTYPE, 2, const_cast<void*>(w), dims, strides,
                           box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -537,6 +538,44 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
     ops.push_back(std::move(op));
     return true;
 }
+// Narrow-output 3x3 convolution (policy projections) on the square-major kernel (hm_pgemm.cuh): the
+// output channels sit on the MMA N side, so 146 / 73 channels cost N = 160 / 80 instead of 256 / 128 rows.
+static bool add_narrow_io(std::vector<Op>& ops, const DenseLayer& L, const DenseIO& io) {
+    const int npad = (L.cout + 15) & ~15;
+    if (L.ksize != 3 || npad > 160 || npad > L.n_rows || getenv("HM_NO_PGEMM") != nullptr) return add_dense_io(ops, L, io);
+    CUtensorMap tm_x, tm_w;
+    if (!make_tm_act3(&tm_x, io.in, io.in_n, io.in_C, io.in_stride_ch)) return false;
+    if (!make_tm_weights(&tm_w, L.w, L.n_rows, L.ksize * L.ksize * L.cpad, npad)) return false;
+    PgemmParams p{};
+    p.n_valid = L.cout;
+    p.npad = npad;
+    p.kblocks = L.cpad / 64;
+    {
+        const int rem = L.cin - (L.cpad / 128 - 1) * 128;
+        p.ksteps_last = std::max(1, std::min(8, (rem + 15) / 16));
+    }
+    p.bias = L.bias;
+    p.out = io.out;
+    p.out_channels = io.out_channels ? io.out_channels : L.cout;
+    p.relu = io.act;
+    p.out_f32 = io.out_f32 ? 1 : 0;
+    if (io.residual != nullptr || io.act > 1) { set_error("pgemm: residual / GELU epilogues are not supported"); return false; }
+    const int smem = pg_smem_bytes(npad);
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (!cuda_ok(cudaFuncSetAttribute(pgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pg_smem_bytes(160)), "pgemm smem attr")) return false;
+        attr_set = true;
+    }
+    const int grid = io.in_n / 2;
+    Op op;
+    op.name = L.name + io.suffix;
+    op.klass = "dense";
+    op.flops = 2.0 * L.macs_per_pos() * io.in_n;
+    op.bytes = 0;
+    op.launch = [p, tm_w, tm_x, grid, smem](cudaStream_t s) { pgemm_kernel<<<grid, PG_THREADS, smem, s>>>(p, tm_w, tm_x); };
+    ops.push_back(std::move(op));
+    return true;
+}
 static bool add_dense(std::vector<Op>& ops, const DenseLayer& L, const act_t* in, int cin_buf,
                       int n_pos, void* out, bool relu, bool out_f32, const char* suffix = "") {
     DenseIO io;
@@ -734,15 +773,19 @@ static bool setup_worker(Engine* e, Worker& w) {
             io.in = w.d_pol_shared + static_cast<size_t>(b) * 192 * 64; io.in_n = B; io.in_C = 192; io.in_stride_ch = 384;
             io.out_channels = POLICY_CH;
             io.out = w.d_pi + static_cast<size_t>(b) * 73 * 64; io.suffix = ".f16";
-            if (!add_dense_io(w.ops_dense_out, net.pol_c2[b], io)) return false;
+            if (!add_narrow_io(w.ops_dense_out, net.pol_c2[b], io)) return false;
             io.out = w.d_logits + static_cast<size_t>(b) * 73 * 64; io.out_f32 = true; io.suffix = "";
-            if (!add_dense_io(w.ops_fused_out, net.pol_c2[b], io)) return false;
+            if (!add_narrow_io(w.ops_fused_out, net.pol_c2[b], io)) return false;
         }
     } else {
         if (!add_dense(ops, net.policy_shared, w.d_trunk, 384, B, w.d_pol_shared, true, false)) return false;
         // reference-shaped post: dense fp16 policy maps, index ch*64+sq (rise_mobile_v3.py:55)
-        if (!add_dense(w.ops_dense_out, net.policy_proj, w.d_pol_shared, 384, B, w.d_pi, false, false, ".f16")) return false;
-        if (!add_dense(w.ops_fused_out, net.policy_proj, w.d_pol_shared, 384, B, w.d_logits, false, true)) return false;
+        DenseIO io;
+        io.in = w.d_pol_shared; io.in_n = B; io.in_C = 384;
+        io.out = w.d_pi; io.suffix = ".f16";
+        if (!add_narrow_io(w.ops_dense_out, net.policy_proj, io)) return false;
+        io.out = w.d_logits; io.out_f32 = true; io.suffix = "";
+        if (!add_narrow_io(w.ops_fused_out, net.policy_proj, io)) return false;
     }
     // ---- fused pre/post ---------------------------------------------------------------------
     {
