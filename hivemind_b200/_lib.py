@@ -24,6 +24,22 @@ class ValueConfig(C.Structure):
     ]
 
 
+class RootPolicy(C.Structure):  # hm_root_policy
+    _fields_ = [
+        ("temperature", C.c_double),
+        ("dirichlet_alpha", C.c_float),
+        ("dirichlet_epsilon", C.c_float),
+        ("noise_seed", C.c_uint64),
+        ("position_hash", C.c_void_p),
+        ("captures", C.c_void_p),
+        ("uniforms", C.c_void_p),
+    ]
+
+
+ROOT_OK, ROOT_RESAMPLED, ROOT_RESAMPLED_FORCED = 0, 1, 2
+ROOT_EMPTY_LIST, ROOT_BAD_WEIGHTS, ROOT_NO_LEGAL_JOINT = -1, -2, -3
+
+
 class KernelTime(C.Structure):
     _fields_ = [("name", C.c_char * 48), ("ms", C.c_float), ("flops", C.c_double), ("bytes", C.c_double)]
 
@@ -45,6 +61,9 @@ SYMBOLS = {
     "hm_engine_run_float": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz]),
     "hm_engine_enqueue_positions": (_i, [_vp, _vp, _sz, _vp, _vp, _sz]),
     "hm_engine_sync_priors": (_i, [_vp, _sz, _pp, _pp, _pp]),
+    "hm_root_policy_apply": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, C.POINTER(RootPolicy), _vp, _vp, _vp]),
+    "hm_engine_enqueue_positions_root": (_i, [_vp, _vp, _sz, _vp, _vp, C.POINTER(RootPolicy), _sz]),
+    "hm_engine_sync_root": (_i, [_vp, _sz, _pp, _pp, _pp, _pp, _pp]),
     "hm_engine_set_value_config": (None, [_vp, C.POINTER(ValueConfig)]),
     "hm_encode_planes": (_i, [_vp, _vp, _sz, _vp, _i]),
     "hm_policy_priors_half": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _vp]),

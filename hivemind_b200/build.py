@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libhm_engine.so")
 OBJ = os.path.join(HERE, "_build")
-SOURCES = ["hm_planes.cu", "hm_layers.cu", "hm_policy.cu", "hm_xboard.cu", "hm_net.cu", "hm_abi.cu", "hm_chunk.cc"]
+SOURCES = ["hm_planes.cu", "hm_layers.cu", "hm_policy.cu", "hm_root.cu", "hm_xboard.cu", "hm_net.cu", "hm_abi.cu", "hm_chunk.cc"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

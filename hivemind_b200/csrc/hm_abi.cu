@@ -216,8 +216,17 @@ int hm_engine_run_float(hm_engine* h, const float* obs, float* value, float* pi_
 }
 
 // ---- fused path -------------------------------------------------------------------------
-int hm_engine_enqueue_positions(hm_engine* h, const hm_packed_pos* pos, size_t n_pos,
-                                const uint32_t* moves, const uint32_t* move_offsets, size_t worker) {
+static bool root_policy_valid(const hm_root_policy* rp) {
+    if (!rp) { set_error("null root policy"); return false; }
+    if (rp->temperature < 0.0 || rp->temperature != rp->temperature) {
+        set_error("Policy temperature must be positive");  // selfplay.cc:168-170
+        return false;
+    }
+    return true;
+}
+
+static int enqueue_positions_impl(hm_engine* h, const hm_packed_pos* pos, size_t n_pos, const uint32_t* moves,
+                                  const uint32_t* move_offsets, const hm_root_policy* rp, size_t worker) {
     HM_TRY
     Worker* w = get_worker(h, worker);
     if (!w || !use_device(h)) return 0;
@@ -241,16 +250,123 @@ int hm_engine_enqueue_positions(hm_engine* h, const hm_packed_pos* pos, size_t n
     bool ok = cuda_ok(cudaMemcpyAsync(w->d_pos, w->h_pos, B * sizeof(hm_packed_pos), cudaMemcpyHostToDevice, s), "H2D pos") &&
               cuda_ok(cudaMemcpyAsync(w->d_offsets, w->h_offsets, (2 * B + 1) * 4, cudaMemcpyHostToDevice, s), "H2D offsets");
     if (ok && n_moves) ok = cuda_ok(cudaMemcpyAsync(w->d_moves, w->h_moves, n_moves * 4, cudaMemcpyHostToDevice, s), "H2D moves");
-    ok = ok && cuda_ok(cudaGraphLaunch(w->graph_fused, s), "graph launch");
+    if (rp) {  // inputs of the root stages ride along with the request
+        RootPolicyArgs a;
+        a.temperature = rp->temperature;
+        a.alpha = rp->dirichlet_alpha;
+        a.epsilon = rp->dirichlet_epsilon;
+        a.seed = rp->noise_seed;
+        if (rp->position_hash && n_pos) {
+            std::memcpy(w->h_hash, rp->position_hash, n_pos * 8);
+            ok = ok && cuda_ok(cudaMemcpyAsync(w->d_hash, w->h_hash, n_pos * 8, cudaMemcpyHostToDevice, s), "H2D hashes");
+            a.hash = w->d_hash;
+        }
+        if (rp->captures && n_moves) {
+            std::memcpy(w->h_captures, rp->captures, n_moves);
+            ok = ok && cuda_ok(cudaMemcpyAsync(w->d_captures, w->h_captures, n_moves, cudaMemcpyHostToDevice, s), "H2D captures");
+            a.captures = w->d_captures;
+        }
+        if (rp->uniforms && n_pos) {
+            std::memcpy(w->h_uniforms, rp->uniforms, n_pos * 3 * 8);
+            ok = ok && cuda_ok(cudaMemcpyAsync(w->d_uniforms, w->h_uniforms, n_pos * 3 * 8, cudaMemcpyHostToDevice, s), "H2D uniforms");
+            a.uniforms = w->d_uniforms;
+        }
+        ok = ok && cuda_ok(cudaGraphLaunch(w->graph_fused, s), "graph launch");
+        if (ok && n_pos) {
+            launch_root_policy(w->d_pos, static_cast<int>(n_pos), w->d_moves, w->d_offsets, w->d_priors, a, w->d_noise,
+                               w->d_picks, w->d_status, s);
+            ok = cuda_ok(cudaGetLastError(), "root policy kernel") &&
+                 cuda_ok(cudaMemcpyAsync(w->h_picks, w->d_picks, n_pos * 2 * 4, cudaMemcpyDeviceToHost, s), "D2H picks") &&
+                 cuda_ok(cudaMemcpyAsync(w->h_status, w->d_status, n_pos * 4, cudaMemcpyDeviceToHost, s), "D2H status");
+        }
+    } else {
+        ok = ok && cuda_ok(cudaGraphLaunch(w->graph_fused, s), "graph launch");
+    }
     if (ok && n_moves) ok = cuda_ok(cudaMemcpyAsync(w->h_priors, w->d_priors, n_moves * 4, cudaMemcpyDeviceToHost, s), "D2H priors");
     ok = ok && cuda_ok(cudaMemcpyAsync(w->h_values, w->d_values, B * 4, cudaMemcpyDeviceToHost, s), "D2H values") &&
          cuda_ok(cudaMemcpyAsync(w->h_raw5, w->d_raw5, B * 5 * 4, cudaMemcpyDeviceToHost, s), "D2H raw");
     if (!ok) return 0;
     w->pending = true;
-    w->pending_kind = 2;
+    w->pending_kind = rp ? 3 : 2;
     w->pending_npos = n_pos;
     w->pending_nmoves = n_moves;
     return 1;
+    HM_CATCH(0)
+}
+
+int hm_engine_enqueue_positions(hm_engine* h, const hm_packed_pos* pos, size_t n_pos,
+                                const uint32_t* moves, const uint32_t* move_offsets, size_t worker) {
+    return enqueue_positions_impl(h, pos, n_pos, moves, move_offsets, nullptr, worker);
+}
+
+int hm_engine_enqueue_positions_root(hm_engine* h, const hm_packed_pos* pos, size_t n_pos,
+                                     const uint32_t* moves, const uint32_t* move_offsets,
+                                     const hm_root_policy* rp, size_t worker) {
+    if (!root_policy_valid(rp)) return 0;
+    return enqueue_positions_impl(h, pos, n_pos, moves, move_offsets, rp, worker);
+}
+
+int hm_engine_sync_root(hm_engine* h, size_t worker, const float** priors, const float** values,
+                        const float** raw, const uint32_t** picks, const int32_t** status) {
+    HM_TRY
+    Worker* w = get_worker(h, worker);
+    if (!w || !use_device(h)) return 0;
+    if (!w->pending || w->pending_kind != 3) { set_error("no root-policy request pending on this worker"); return 0; }
+    w->pending = false;
+    if (!cuda_ok(cudaStreamSynchronize(w->stream), "stream sync")) return 0;
+    if (priors) *priors = w->h_priors;
+    if (values) *values = w->h_values;
+    if (raw) *raw = w->h_raw5;
+    if (picks) *picks = w->h_picks;
+    if (status) *status = w->h_status;
+    return 1;
+    HM_CATCH(0)
+}
+
+int hm_root_policy_apply(hm_engine* h, const hm_packed_pos* pos, size_t n_pos, const uint32_t* moves,
+                         const uint32_t* move_offsets, float* priors, const hm_root_policy* rp,
+                         float* noise_out, uint32_t* picks, int32_t* status) {
+    HM_TRY
+    if (!h || !pos || !move_offsets || !priors) { set_error("null argument"); return 0; }
+    if (!root_policy_valid(rp)) return 0;
+    if (n_pos == 0) return 1;
+    if (!use_device(h)) return 0;
+    std::lock_guard<std::mutex> lock(h->util_mutex);
+    const size_t n_moves = move_offsets[2 * n_pos];
+    if (n_moves > 0 && !moves) { set_error("null move list"); return 0; }
+    for (size_t i = 0; i < 2 * n_pos; ++i)
+        if (move_offsets[i] > move_offsets[i + 1]) { set_error("move offsets must be non-decreasing"); return 0; }
+    DevBuf<hm_packed_pos> dpos;
+    DevBuf<uint32_t> dm, doff, dpick;
+    DevBuf<float> dp, dn;
+    DevBuf<uint8_t> dc;
+    DevBuf<uint64_t> dh;
+    DevBuf<double> du;
+    DevBuf<int32_t> dst;
+    if (!dpos.alloc(n_pos) || !dm.alloc(n_moves) || !doff.alloc(2 * n_pos + 1) || !dp.alloc(n_moves) || !dn.alloc(n_moves) ||
+        !dc.alloc(n_moves) || !dh.alloc(n_pos) || !du.alloc(3 * n_pos) || !dpick.alloc(2 * n_pos) || !dst.alloc(n_pos)) return 0;
+    cudaStream_t s = h->e.util_stream;
+    RootPolicyArgs a;
+    a.temperature = rp->temperature;
+    a.alpha = rp->dirichlet_alpha;
+    a.epsilon = rp->dirichlet_epsilon;
+    a.seed = rp->noise_seed;
+    bool ok = cuda_ok(cudaMemcpyAsync(dpos.p, pos, n_pos * sizeof(hm_packed_pos), cudaMemcpyHostToDevice, s), "H2D") &&
+              cuda_ok(cudaMemcpyAsync(doff.p, move_offsets, (2 * n_pos + 1) * 4, cudaMemcpyHostToDevice, s), "H2D") &&
+              cuda_ok(cudaMemsetAsync(dn.p, 0, std::max<size_t>(n_moves, 1) * 4, s), "memset");
+    if (ok && n_moves) ok = cuda_ok(cudaMemcpyAsync(dm.p, moves, n_moves * 4, cudaMemcpyHostToDevice, s), "H2D") &&
+                            cuda_ok(cudaMemcpyAsync(dp.p, priors, n_moves * 4, cudaMemcpyHostToDevice, s), "H2D");
+    if (ok && rp->position_hash) { ok = cuda_ok(cudaMemcpyAsync(dh.p, rp->position_hash, n_pos * 8, cudaMemcpyHostToDevice, s), "H2D"); a.hash = dh.p; }
+    if (ok && rp->captures && n_moves) { ok = cuda_ok(cudaMemcpyAsync(dc.p, rp->captures, n_moves, cudaMemcpyHostToDevice, s), "H2D"); a.captures = dc.p; }
+    if (ok && rp->uniforms) { ok = cuda_ok(cudaMemcpyAsync(du.p, rp->uniforms, 3 * n_pos * 8, cudaMemcpyHostToDevice, s), "H2D"); a.uniforms = du.p; }
+    if (!ok) return 0;
+    launch_root_policy(dpos.p, static_cast<int>(n_pos), dm.p, doff.p, dp.p, a, dn.p, dpick.p, dst.p, s);
+    if (!cuda_ok(cudaGetLastError(), "root policy kernel")) return 0;
+    if (n_moves) ok = cuda_ok(cudaMemcpyAsync(priors, dp.p, n_moves * 4, cudaMemcpyDeviceToHost, s), "D2H");
+    if (ok && noise_out && n_moves) ok = cuda_ok(cudaMemcpyAsync(noise_out, dn.p, n_moves * 4, cudaMemcpyDeviceToHost, s), "D2H");
+    if (ok && picks && rp->uniforms) ok = cuda_ok(cudaMemcpyAsync(picks, dpick.p, 2 * n_pos * 4, cudaMemcpyDeviceToHost, s), "D2H");
+    if (ok && status) ok = cuda_ok(cudaMemcpyAsync(status, dst.p, n_pos * 4, cudaMemcpyDeviceToHost, s), "D2H");
+    return ok && cuda_ok(cudaStreamSynchronize(s), "root policy sync") ? 1 : 0;
     HM_CATCH(0)
 }
 

@@ -57,4 +57,20 @@ void launch_shape_values_raw5(const float* raw5, int n, hm_value_config cfg, flo
 void launch_shape_values_half(const __half* value, const __half* wdl, const __half* ml, int n,
                               hm_value_config cfg, float* out, cudaStream_t s);
 
+// ---- root policy (hm_root.cu): temperature, Dirichlet noise, joint-action sampling --------------
+struct RootPolicyArgs {
+    double temperature = 0.0;
+    float alpha = 0.0f, epsilon = 0.0f;
+    uint64_t seed = 0;
+    const uint64_t* hash = nullptr;     // device [n_pos]
+    const uint8_t* captures = nullptr;  // device, per move
+    const double* uniforms = nullptr;   // device [n_pos][3]
+};
+// priors updated in place; noise = scratch of the same size as priors (required when the noise stage
+// runs); picks [n_pos][2] / status [n_pos] may be null
+void launch_root_policy(const hm_packed_pos* pos, int n_pos, const uint32_t* moves, const uint32_t* offsets,
+                        float* priors, const RootPolicyArgs& a, float* noise, uint32_t* picks, int32_t* status,
+                        cudaStream_t s);
+
+
 }  // namespace hm

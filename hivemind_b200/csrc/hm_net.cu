@@ -712,13 +712,18 @@ static bool setup_worker(Engine* e, Worker& w) {
               dev_alloc(w, &w.d_trunk, nb * 384 * 64) && dev_alloc(w, &w.d_pol_shared, nb * 384 * 64) &&
               dev_alloc(w, &w.d_logits, nb * POLICY_CH * 64) && dev_alloc(w, &w.d_pi, nb * POLICY_CH * 64) &&
               dev_alloc(w, &w.d_vfeat, nb * 16 * 64) && dev_alloc(w, &w.d_raw5, nb * 5) &&
-              dev_alloc(w, &w.d_value_h, nb) && dev_alloc(w, &w.d_wdl_h, nb * 3) && dev_alloc(w, &w.d_ml_h, nb);
+              dev_alloc(w, &w.d_value_h, nb) && dev_alloc(w, &w.d_wdl_h, nb * 3) && dev_alloc(w, &w.d_ml_h, nb) &&
+              dev_alloc(w, &w.d_captures, w.move_cap) && dev_alloc(w, &w.d_noise, w.move_cap) &&
+              dev_alloc(w, &w.d_hash, nb) && dev_alloc(w, &w.d_uniforms, nb * 3) &&
+              dev_alloc(w, &w.d_picks, nb * 2) && dev_alloc(w, &w.d_status, nb);
     ok = ok && host_alloc(w, &w.h_pos, nb) && host_alloc(w, &w.h_moves, w.move_cap) &&
          host_alloc(w, &w.h_offsets, 2 * nb + 1) && host_alloc(w, &w.h_priors, w.move_cap) &&
          host_alloc(w, &w.h_values, nb) && host_alloc(w, &w.h_raw5, nb * 5) &&
          host_alloc(w, &w.h_obs, nb * HM_NB_INPUT_VALUES) && host_alloc(w, &w.h_value, nb) &&
          host_alloc(w, &w.h_wdl, nb * 3) && host_alloc(w, &w.h_ml, nb) &&
-         host_alloc(w, &w.h_pi_a, nb * HM_NB_POLICY_VALUES) && host_alloc(w, &w.h_pi_b, nb * HM_NB_POLICY_VALUES);
+         host_alloc(w, &w.h_pi_a, nb * HM_NB_POLICY_VALUES) && host_alloc(w, &w.h_pi_b, nb * HM_NB_POLICY_VALUES) &&
+         host_alloc(w, &w.h_captures, w.move_cap) && host_alloc(w, &w.h_hash, nb) &&
+         host_alloc(w, &w.h_uniforms, nb * 3) && host_alloc(w, &w.h_picks, nb * 2) && host_alloc(w, &w.h_status, nb);
     if (!ok || !kernels_prepare()) return false;
 
     // ---- stem + residual trunk + value head + shared policy conv -----------------------------

@@ -111,7 +111,7 @@ struct Worker {
     cudaStream_t side_stream = nullptr;   // captured only: the value-head branch of the graphs
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool pending = false;
-    int pending_kind = 0;  // 1 = dense half request, 2 = packed positions request
+    int pending_kind = 0;  // 1 = dense half request, 2 = packed positions request, 3 = positions + root stages
     size_t pending_npos = 0, pending_nmoves = 0;
 
     // device arena
@@ -120,6 +120,14 @@ struct Worker {
     uint32_t* d_offsets = nullptr;
     float* d_priors = nullptr;
     float* d_values = nullptr;
+    // root-policy stages (hm_root.cu): per-move capture flags / noise scratch, per-position hashes,
+    // uniforms [B][3], picks [B][2], status [B]
+    uint8_t* d_captures = nullptr;
+    float* d_noise = nullptr;
+    uint64_t* d_hash = nullptr;
+    double* d_uniforms = nullptr;
+    uint32_t* d_picks = nullptr;
+    int32_t* d_status = nullptr;
     act_t* d_planes = nullptr;      // [B][74][64] network input (NCHW, the reference's obs layout)
     act_t* d_trunk = nullptr;       // [B][384][64], updated in place by the trunk kernels
     act_t* d_pol_shared = nullptr;  // [B][384][64]
@@ -140,6 +148,11 @@ struct Worker {
     float* h_priors = nullptr;
     float* h_values = nullptr;
     float* h_raw5 = nullptr;
+    uint8_t* h_captures = nullptr;
+    uint64_t* h_hash = nullptr;
+    double* h_uniforms = nullptr;
+    uint32_t* h_picks = nullptr;
+    int32_t* h_status = nullptr;
     __half* h_obs = nullptr;        // staging of runInference's float -> half conversion
     __half *h_value = nullptr, *h_wdl = nullptr, *h_ml = nullptr, *h_pi_a = nullptr,
            *h_pi_b = nullptr;

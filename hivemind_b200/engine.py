@@ -12,7 +12,7 @@ from typing import Optional
 import numpy as np
 
 from . import _lib
-from ._lib import NB_INPUT_VALUES, NB_POLICY_VALUES, KernelTime, ValueConfig
+from ._lib import NB_INPUT_VALUES, NB_POLICY_VALUES, KernelTime, RootPolicy, ValueConfig
 
 BATCH_SIZE = 8          # engine/src/search/search_params.h:26
 NUM_SEARCH_THREADS = 4  # engine/src/search/search_params.h:30
@@ -137,6 +137,77 @@ class Engine:
         if not self.enqueuePositions(pos, moves, offsets, workerIndex):
             return None
         return self.synchronizePriors(workerIndex)
+
+    # ---- root policy on the device (include/hm_engine.h "root policy"): temperature
+    # (selfplay.cc:167-185), root Dirichlet noise (node.h:288-315), joint-action sampling
+    # (selfplay.cc:301-376) ----------------------------------------------------------------
+    def _root_policy(self, n_pos, n_moves, temperature, dirichlet_alpha, dirichlet_epsilon, noise_seed,
+                     position_hash, captures, uniforms):
+        keep = []
+
+        def arr(a, dtype, size):
+            if a is None:
+                return None
+            a = np.ascontiguousarray(a, dtype)
+            if a.size != size:
+                raise ValueError(f"expected {size} elements, got {a.size}")
+            keep.append(a)
+            return a.ctypes.data
+
+        rp = RootPolicy(float(temperature), float(dirichlet_alpha), float(dirichlet_epsilon), int(noise_seed),
+                        arr(position_hash, np.uint64, n_pos), arr(captures, np.uint8, n_moves),
+                        arr(uniforms, np.float64, 3 * n_pos))
+        return rp, keep
+
+    def rootPolicyApply(self, pos, moves, offsets, priors, temperature=0.0, dirichlet_alpha=0.0, dirichlet_epsilon=0.0,
+                        noise_seed=0, position_hash=None, captures=None, uniforms=None):
+        """Stand-alone root stages on host priors -> (priors, noise, picks[n,2], status[n]) or None."""
+        pos = np.ascontiguousarray(pos)
+        moves = np.ascontiguousarray(moves, np.uint32)
+        offsets = np.ascontiguousarray(offsets, np.uint32)
+        n = pos.shape[0]
+        if pos.dtype.itemsize != 256 or offsets.size != 2 * n + 1:
+            return None
+        out = np.array(priors, np.float32, copy=True)
+        n_moves = int(offsets[-1])
+        if out.size != n_moves:
+            return None
+        rp, keep = self._root_policy(n, n_moves, temperature, dirichlet_alpha, dirichlet_epsilon, noise_seed,
+                                     position_hash, captures, uniforms)
+        noise = np.zeros(n_moves, np.float32)
+        picks = np.zeros((n, 2), np.uint32)
+        status = np.zeros(n, np.int32)
+        ok = self._L.hm_root_policy_apply(self._h, pos.ctypes.data, n, moves.ctypes.data, offsets.ctypes.data,
+                                          out.ctypes.data, C.byref(rp), noise.ctypes.data, picks.ctypes.data,
+                                          status.ctypes.data)
+        del keep
+        return (out, noise, picks, status) if ok else None
+
+    def enqueuePositionsRoot(self, pos, moves, offsets, workerIndex: int = 0, **root) -> bool:
+        pos = np.ascontiguousarray(pos)
+        moves = np.ascontiguousarray(moves, np.uint32)
+        offsets = np.ascontiguousarray(offsets, np.uint32)
+        if pos.dtype.itemsize != 256 or offsets.size != 2 * pos.shape[0] + 1:
+            return False
+        self._pending_n = (pos.shape[0], int(offsets[-1]))
+        rp, keep = self._root_policy(pos.shape[0], int(offsets[-1]), root.get("temperature", 0.0),
+                                     root.get("dirichlet_alpha", 0.0), root.get("dirichlet_epsilon", 0.0),
+                                     root.get("noise_seed", 0), root.get("position_hash"), root.get("captures"),
+                                     root.get("uniforms"))
+        ok = bool(self._L.hm_engine_enqueue_positions_root(self._h, pos.ctypes.data, pos.shape[0], moves.ctypes.data,
+                                                           offsets.ctypes.data, C.byref(rp), workerIndex))
+        del keep  # the ABI copies every input into engine-owned pinned memory before returning
+        return ok
+
+    def synchronizeRoot(self, workerIndex: int = 0):
+        """-> (priors, values, raw, picks[n_pos,2] u32, status[n_pos] i32) or None."""
+        p = [C.c_void_p() for _ in range(5)]
+        if not self._L.hm_engine_sync_root(self._h, workerIndex, *[C.byref(x) for x in p]):
+            return None
+        n_pos, n_moves = self._pending_n
+        priors = _view(p[0], (n_moves,), np.float32) if n_moves else np.empty(0, np.float32)
+        return (priors, _view(p[1], (n_pos,), np.float32), _view(p[2], (n_pos, 5), np.float32),
+                _view(p[3], (n_pos, 2), np.uint32), _view(p[4], (n_pos,), np.int32))
 
     def setValueConfig(self, enable_wdl_eval=True, wdl_value_weight=0.25, moves_left_discount=0.005, draw_contempt=0.0):
         cfg = ValueConfig(int(enable_wdl_eval), wdl_value_weight, moves_left_discount, draw_contempt)

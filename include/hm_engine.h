@@ -156,6 +156,58 @@ int hm_engine_sync_priors(hm_engine* e, size_t worker, const float** priors,
 
 void hm_engine_set_value_config(hm_engine* e, const hm_value_config* cfg);
 
+/* ---- root policy on the device: temperature, Dirichlet noise, joint-action sampling ---- */
+
+/* Replaces the host loops that post-process root / opening priors in the reference:
+ *   apply_temperature             tools/selfplay.cc:167-185 (raw-policy openings, :283-299)
+ *   root Dirichlet noise          search/node.h:288-315 (Node::try_init_and_expand, depth 0)
+ *   sample_raw_policy_action      tools/selfplay.cc:301-376, legality = JointActionCandidate
+ *                                 (environment/joint_action.h:14-110)
+ * Stages run in that order; each is skipped when its inputs are absent. */
+typedef struct hm_root_policy {
+    double temperature;            /* > 0: p_i = pow(max(0,p_i), 1/T) renormalised; 0 = skip; < 0 = error */
+    float dirichlet_alpha;         /* RuntimeConfig::rootDirichletAlpha   (search_params.h:292) */
+    float dirichlet_epsilon;       /* RuntimeConfig::rootDirichletEpsilon (search_params.h:293); noise runs when
+                                      alpha > 0, epsilon > 0, position_hash != NULL and the list has > 1 move */
+    uint64_t noise_seed;           /* RuntimeConfig::rootNoiseSeed; key = seed ^ position_hash[i] ^ board salt
+                                      (node.h:295-296).  The variates are Gamma(alpha,1) as in the reference but come
+                                      from a counter-based generator, not mt19937_64: same distribution, other stream */
+    const uint64_t* position_hash; /* [n_pos] or NULL */
+    const uint8_t* captures;       /* one flag per move (same offsets as `moves`): Board::is_capture, 0 for MOVE_NONE
+                                      (selfplay.cc:337-347); NULL = no move captures */
+    const double* uniforms;        /* [n_pos][3] or NULL (no sampling): the std::generate_canonical<double,53> draws
+                                      std::discrete_distribution makes for board A, board B and the legal-pair
+                                      resample.  A list of < 2 entries consumes no draw in the reference, nor does a
+                                      resample over a single legal pair: see INTEGRATION.md for the host recipe that
+                                      keeps a std::mt19937_64 in step */
+} hm_root_policy;
+
+#define HM_ROOT_OK 0
+#define HM_ROOT_RESAMPLED 1          /* independent picks were an illegal sit; drawn again from the legal pairs
+                                        (uniforms[3i+2] was consumed) */
+#define HM_ROOT_RESAMPLED_FORCED 2   /* the same, but only ONE pair was legal: taken without a draw, as
+                                        std::discrete_distribution of one weight does */
+#define HM_ROOT_EMPTY_LIST (-1)      /* a board's move list was empty (the reference always appends MOVE_NONE) */
+#define HM_ROOT_BAD_WEIGHTS (-2)     /* a prior list did not sum to a positive finite number */
+#define HM_ROOT_NO_LEGAL_JOINT (-3)  /* selfplay.cc:369-371 throws "Raw policy produced no legal joint action" */
+
+/* Stand-alone stage on HOST priors (same offsets as `moves`); priors are updated in place.
+ * picks: [n_pos][2] indices into board A's and board B's move list; status: [n_pos] HM_ROOT_*;
+ * noise_out: the raw gamma variates per move (for inspection).  picks/status/noise_out may be NULL. */
+int hm_root_policy_apply(hm_engine* e, const hm_packed_pos* pos, size_t n_pos, const uint32_t* moves,
+                         const uint32_t* move_offsets, float* priors, const hm_root_policy* rp,
+                         float* noise_out, uint32_t* picks, int32_t* status);
+
+/* Fused: hm_engine_enqueue_positions followed by the root stages on the device priors, one
+ * stream, no host round trip between the forward and the sampler (selfplay.cc:240-260 runs a
+ * whole fp32 runInference per opening ply for this). */
+int hm_engine_enqueue_positions_root(hm_engine* e, const hm_packed_pos* pos, size_t n_pos,
+                                     const uint32_t* moves, const uint32_t* move_offsets,
+                                     const hm_root_policy* rp, size_t worker);
+/* As hm_engine_sync_priors, plus picks [n_pos][2] and status [n_pos] (engine-owned pinned memory). */
+int hm_engine_sync_root(hm_engine* e, size_t worker, const float** priors, const float** values,
+                        const float** raw, const uint32_t** picks, const int32_t** status);
+
 /* ---- stand-alone stages (parity checks and benches) ---------------------------- */
 
 /* board_to_planes for n packed positions -> [n,74,8,8] of `dtype` in HOST memory

@@ -126,6 +126,42 @@ public:
                       hm_engine_sync_priors(m_handle, workerIndex, &out.priors, &out.values, &out.raw) != 0,
                   "synchronizePriors");
     }
+    // ---- root policy on the device: apply_temperature (selfplay.cc:167-185), root Dirichlet noise
+    // (node.h:288-315), sample_raw_policy_action's joint sampling (selfplay.cc:349-392) ----
+    struct RootOutputs : PriorOutputs {
+        const uint32_t* picks = nullptr;  // [nPos][2]: index into board A's / board B's move list
+        const int32_t* status = nullptr;  // [nPos] HM_ROOT_*
+    };
+    bool enqueuePositionsRoot(const hm_packed_pos* pos, size_t nPos, const uint32_t* moves,
+                              const uint32_t* moveOffsets, const hm_root_policy& root, size_t workerIndex = 0) {
+        return ok(m_handle != nullptr &&
+                      hm_engine_enqueue_positions_root(m_handle, pos, nPos, moves, moveOffsets, &root, workerIndex) != 0,
+                  "enqueuePositionsRoot");
+    }
+    bool synchronizeRoot(RootOutputs& out, size_t workerIndex = 0) {
+        return ok(m_handle != nullptr && hm_engine_sync_root(m_handle, workerIndex, &out.priors, &out.values, &out.raw,
+                                                             &out.picks, &out.status) != 0,
+                  "synchronizeRoot");
+    }
+    // The canonical doubles std::discrete_distribution would take from `randomEngine` in
+    // sample_raw_policy_action, WITHOUT advancing it past what the reference consumes: u[0] / u[1] are
+    // drawn only for lists of >= 2 entries (board B first: g++ evaluates the two arguments of
+    // selfplay.cc:365 right to left), u[2] comes from a copy of the engine.  After synchronizeRoot call
+    // commitRootDraw(randomEngine, status) — it takes the third draw for real iff the device used it.
+    template <class URNG>
+    static void drawRootUniforms(URNG& randomEngine, size_t nA, size_t nB, double u[3], bool boardBFirst = true) {
+        u[0] = u[1] = u[2] = 0.0;
+        for (int k = 0; k < 2; ++k) {
+            const int b = boardBFirst ? 1 - k : k;
+            if ((b ? nB : nA) >= 2) u[b] = canonical(randomEngine);
+        }
+        URNG peek = randomEngine;
+        u[2] = canonical(peek);
+    }
+    template <class URNG>
+    static void commitRootDraw(URNG& randomEngine, int32_t status) {
+        if (status == HM_ROOT_RESAMPLED) (void)canonical(randomEngine);
+    }
     void setValueConfig(const hm_value_config& cfg) {
         if (m_handle != nullptr) hm_engine_set_value_config(m_handle, &cfg);
     }
@@ -133,6 +169,12 @@ public:
     int getDeviceId() const { return m_deviceId; }
 
 private:
+    // std::generate_canonical<double, 53> for a 64-bit engine: one draw, x / 2^64 (bits/random.tcc)
+    template <class URNG>
+    static double canonical(URNG& e) {
+        const double r = static_cast<double>(e() - URNG::min()) / 18446744073709551616.0;
+        return r < 1.0 ? r : 0.99999999999999988898;
+    }
     // the reference reports failures on stderr and returns false (engine.cc:217-248, 573-679)
     static void report(const char* what) { std::cerr << "[ERROR] " << what << ": " << hm_last_error() << std::endl; }
     static bool ok(bool cond, const char* what) {

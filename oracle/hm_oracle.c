@@ -405,3 +405,159 @@ float hmo_shape_value_half(uint16_t value, const uint16_t* wdl, const uint16_t* 
     if (moves_left) ml = hmo_half_to_float(*moves_left);
     return hmo_shape_value(hmo_half_to_float(value), wdl ? w : NULL, moves_left ? &ml : NULL, cfg);
 }
+
+/* ===================================================================================
+ * Root policy stages (tools/selfplay.cc:167-185,301-376; search/node.h:288-315;
+ * environment/joint_action.h:14-110)
+ * =================================================================================== */
+#include <stdlib.h>
+
+int hmo_apply_temperature(float* p, size_t n, double temperature) {
+    if (n == 0 || !(temperature > 0.0)) return 0;              /* selfplay.cc:168-170 */
+    const double exponent = 1.0 / temperature;
+    double total = 0.0;
+    for (size_t i = 0; i < n; ++i) {                           /* :173-176 */
+        p[i] = (float)pow((double)(p[i] > 0.0f ? p[i] : 0.0f), exponent);
+        total += p[i];
+    }
+    if (!isfinite(total) || total <= 0.0) {                    /* :177-181 */
+        const float uniform = 1.0f / (float)n;
+        for (size_t i = 0; i < n; ++i) p[i] = uniform;
+        return 1;
+    }
+    for (size_t i = 0; i < n; ++i) p[i] = (float)(p[i] / total); /* :182-184 */
+    return 1;
+}
+
+void hmo_dirichlet_mix(float* p, const float* noise, size_t n, float epsilon) {
+    if (n <= 1) return;                                        /* node.h:292-294 */
+    volatile float total = 0.0f;                               /* volatile: one rounding per add */
+    for (size_t i = 0; i < n; ++i) total = total + noise[i];   /* :299-303 */
+    if (total <= 0.0f) return;                                 /* :304-306 */
+    const float eps = epsilon < 0.0f ? 0.0f : (epsilon > 1.0f ? 1.0f : epsilon);
+    for (size_t i = 0; i < n; ++i) {                           /* :308-311, op by op, no contraction */
+        volatile float keep = (1.0f - eps) * p[i];
+        volatile float scaled = eps * noise[i];
+        volatile float add = scaled / total;
+        p[i] = keep + add;
+    }
+}
+
+size_t hmo_discrete_pick_f64(const double* w, size_t n, double u) {
+    if (n < 2) return 0;                                       /* _M_prob.size() < 2: no table, no draw */
+    double* cp = (double*)malloc(n * sizeof(double));
+    double sum = 0.0;
+    for (size_t i = 0; i < n; ++i) sum += w[i];                /* std::accumulate(.., 0.0) */
+    double run = 0.0;
+    for (size_t i = 0; i < n; ++i) { run += w[i] / sum; cp[i] = run; }  /* __normalize, partial_sum */
+    cp[n - 1] = 1.0;
+    size_t lo = 0, len = n;                                    /* std::lower_bound(cp, cp+n, u) */
+    while (len > 0) {
+        const size_t half = len >> 1;
+        if (cp[lo + half] < u) { lo += half + 1; len -= half + 1; } else len = half;
+    }
+    free(cp);
+    return lo;
+}
+
+size_t hmo_discrete_pick_f32(const float* p, size_t n, double u) {
+    if (n < 2) return 0;
+    double* w = (double*)malloc(n * sizeof(double));
+    for (size_t i = 0; i < n; ++i) w[i] = (double)p[i];        /* vector<double>(first, last) */
+    const size_t r = hmo_discrete_pick_f64(w, n, u);
+    free(w);
+    return r;
+}
+
+/* joint_action.h:14-32 */
+static int double_sit_legal(int tadv, int a_on, int b_on) { return tadv && (a_on != b_on); }
+static int single_pass_legal(int tadv, int a_on, int b_on, int partner_capture) {
+    return tadv || !(a_on && b_on) || partner_capture;
+}
+/* joint_action.h:84-110: 1 when jointPrior >= 0 */
+static int joint_is_legal(uint32_t m_a, uint32_t m_b, int cap_a, int cap_b, int tadv, int a_on, int b_on,
+                          int a_can, int b_can) {
+    const int sits_a = m_a == 0u, sits_b = m_b == 0u;
+    if (sits_a && sits_b) return double_sit_legal(tadv, a_on, b_on);
+    if (sits_a && a_can) return single_pass_legal(tadv, a_on, b_on, cap_b);
+    if (sits_b && b_can) return single_pass_legal(tadv, a_on, b_on, cap_a);
+    return 1;
+}
+
+int hmo_sample_joint(const hm_packed_pos* pos, const uint32_t* moves_a, const float* p_a, const uint8_t* cap_a,
+                     size_t n_a, const uint32_t* moves_b, const float* p_b, const uint8_t* cap_b, size_t n_b,
+                     const double* u, uint32_t* pick_a, uint32_t* pick_b) {
+    *pick_a = *pick_b = 0;
+    if (n_a == 0 || n_b == 0) return HM_ROOT_EMPTY_LIST;
+    const uint8_t f_a = pos->board[0].flags, f_b = pos->board[1].flags;
+    const int team_black = (f_a & HM_FLAG_TEAM_BLACK) != 0, tadv = (f_a & HM_FLAG_TIME_ADVANTAGE) != 0;
+    const int a_on = ((f_a & HM_FLAG_STM_BLACK) != 0) == team_black;      /* selfplay.cc:310 */
+    const int b_on = ((f_b & HM_FLAG_STM_BLACK) != 0) != team_black;      /* :311 */
+    const int a_can = a_on && n_a > 1, b_can = b_on && n_b > 1;           /* :353-354 */
+    for (int b = 0; b < 2; ++b) {
+        const float* p = b ? p_b : p_a;
+        const size_t n = b ? n_b : n_a;
+        double s = 0.0;
+        for (size_t i = 0; i < n; ++i) s += p[i];
+        if (n >= 2 && (!(s > 0.0) || !isfinite(s))) return HM_ROOT_BAD_WEIGHTS;
+    }
+#define CAP(c, m, i) ((m)[i] != 0u && (c) != NULL && (c)[i] != 0)          /* :337-347 */
+#define LEGAL(i, j) joint_is_legal(moves_a[i], moves_b[j], CAP(cap_a, moves_a, i), CAP(cap_b, moves_b, j), \
+                                   tadv, a_on, b_on, a_can, b_can)
+    size_t i_a = hmo_discrete_pick_f32(p_a, n_a, u[0]);                    /* :363-365 */
+    size_t i_b = hmo_discrete_pick_f32(p_b, n_b, u[1]);
+    int st = HM_ROOT_OK;
+    if (!LEGAL(i_a, i_b)) {                                                /* :370-392 */
+        size_t cap_pairs = n_a * n_b, n_legal = 0;
+        size_t* pa = (size_t*)malloc(cap_pairs * sizeof(size_t));
+        size_t* pb = (size_t*)malloc(cap_pairs * sizeof(size_t));
+        double* w = (double*)malloc(cap_pairs * sizeof(double));
+        double total = 0.0;
+        for (size_t i = 0; i < n_a; ++i)
+            for (size_t j = 0; j < n_b; ++j) {
+                if (!LEGAL(i, j)) continue;
+                pa[n_legal] = i; pb[n_legal] = j;
+                w[n_legal] = (double)p_a[i] * (double)p_b[j];
+                total += w[n_legal];
+                ++n_legal;
+            }
+        if (!(total > 0.0) || !isfinite(total)) {
+            st = HM_ROOT_NO_LEGAL_JOINT;
+        } else {
+            const size_t k = hmo_discrete_pick_f64(w, n_legal, u[2]);
+            i_a = pa[k]; i_b = pb[k];
+            st = n_legal >= 2 ? HM_ROOT_RESAMPLED : HM_ROOT_RESAMPLED_FORCED;
+        }
+        free(pa); free(pb); free(w);
+    }
+#undef LEGAL
+#undef CAP
+    *pick_a = (uint32_t)i_a; *pick_b = (uint32_t)i_b;
+    return st;
+}
+
+/* MT19937-64 (Matsumoto & Nishimura) = std::mt19937_64; generate_canonical<double,53> takes ONE
+ * 64-bit draw: double(x) / 2^64, and nextafter(1,0) if that rounds to 1 (bits/random.tcc). */
+void hmo_mt19937_64_canonical(uint64_t seed, size_t n, double* out) {
+    uint64_t mt[312];
+    mt[0] = seed;
+    for (int i = 1; i < 312; ++i) mt[i] = 6364136223846793005ULL * (mt[i - 1] ^ (mt[i - 1] >> 62)) + (uint64_t)i;
+    int idx = 312;
+    for (size_t k = 0; k < n; ++k) {
+        if (idx >= 312) {
+            for (int i = 0; i < 312; ++i) {
+                const uint64_t x = (mt[i] & 0xFFFFFFFF80000000ULL) | (mt[(i + 1) % 312] & 0x7FFFFFFFULL);
+                mt[i] = mt[(i + 156) % 312] ^ (x >> 1) ^ ((x & 1ULL) ? 0xB5026F5AA96619E9ULL : 0ULL);
+            }
+            idx = 0;
+        }
+        uint64_t x = mt[idx++];
+        x ^= (x >> 29) & 0x5555555555555555ULL;
+        x ^= (x << 17) & 0x71D67FFFEDA60000ULL;
+        x ^= (x << 37) & 0xFFF7EEE000000000ULL;
+        x ^= (x >> 43);
+        double r = (double)x / 18446744073709551616.0;
+        if (r >= 1.0) r = nextafter(1.0, 0.0);
+        out[k] = r;
+    }
+}

@@ -64,6 +64,27 @@ void hmo_batch_priors_f16(const uint16_t* logits_a, const uint16_t* logits_b,
                           const hm_packed_pos* pos, size_t n_pos, const uint32_t* moves,
                           const uint32_t* move_offsets, float* priors_out);
 
+/* ---- root policy stages ---------------------------------------------
+ * Pinned against the reference through oracle/_ref (hmref_sample_joint runs the reference's own
+ * JointActionCandidate with the real std::discrete_distribution / std::mt19937_64) and the committed
+ * fixture tests/golden/root_policy.npz (oracle/make_golden_root.py). */
+/* tools/selfplay.cc:167-185 apply_temperature; returns 0 if temperature <= 0 (the reference throws) */
+int hmo_apply_temperature(float* p, size_t n, double temperature);
+/* search/node.h:301-311: total = sum(noise) in float, p = (1-eps)*p + eps*noise/total (eps clamped) */
+void hmo_dirichlet_mix(float* p, const float* noise, size_t n, float epsilon);
+/* std::discrete_distribution<size_t>(p, p+n) drawn with the canonical double u, as libstdc++ does it
+ * (bits/random.tcc _M_initialize / operator()); n < 2 returns 0 and uses no draw */
+size_t hmo_discrete_pick_f32(const float* p, size_t n, double u);
+size_t hmo_discrete_pick_f64(const double* w, size_t n, double u);
+/* tools/selfplay.cc:301-376 sample_raw_policy_action after the priors are known: independent picks,
+ * legality by environment/joint_action.h:14-110, resample over the legal pairs.  u = {uA, uB, uJoint}.
+ * Returns HM_ROOT_OK / HM_ROOT_RESAMPLED / HM_ROOT_RESAMPLED_FORCED / HM_ROOT_NO_LEGAL_JOINT / HM_ROOT_EMPTY_LIST / HM_ROOT_BAD_WEIGHTS. */
+int hmo_sample_joint(const hm_packed_pos* pos, const uint32_t* moves_a, const float* p_a, const uint8_t* cap_a,
+                     size_t n_a, const uint32_t* moves_b, const float* p_b, const uint8_t* cap_b, size_t n_b,
+                     const double* u, uint32_t* pick_a, uint32_t* pick_b);
+/* std::generate_canonical<double,53> on std::mt19937_64(seed): n successive draws (restated MT19937-64) */
+void hmo_mt19937_64_canonical(uint64_t seed, size_t n, double* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -95,7 +95,47 @@ class Oracle:
         L.hmo_priors_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
         L.hmo_batch_priors_f16.argtypes = [C.c_void_p] * 3 + [C.c_size_t] + [C.c_void_p] * 3
         L.hmo_policy_tables.argtypes = [C.c_void_p, C.c_void_p]
+        L.hmo_apply_temperature.argtypes = [C.c_void_p, C.c_size_t, C.c_double]
+        L.hmo_dirichlet_mix.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_float]
+        L.hmo_discrete_pick_f32.restype = C.c_size_t
+        L.hmo_discrete_pick_f32.argtypes = [C.c_void_p, C.c_size_t, C.c_double]
+        L.hmo_sample_joint.argtypes = [C.c_void_p] * 4 + [C.c_size_t] + [C.c_void_p] * 3 + [C.c_size_t] + [C.c_void_p] * 3
+        L.hmo_mt19937_64_canonical.argtypes = [C.c_uint64, C.c_size_t, C.c_void_p]
         L.hmo_policy_init()
+
+    # ---- root policy stages (selfplay.cc:167-185,301-376; node.h:288-315) ----
+    def apply_temperature(self, p, temperature: float) -> np.ndarray:
+        out = np.array(p, np.float32, copy=True)
+        if not self.lib.hmo_apply_temperature(_ptr(out), out.size, temperature):
+            raise ValueError("Policy temperature must be positive")
+        return out
+
+    def dirichlet_mix(self, p, noise, epsilon: float) -> np.ndarray:
+        out = np.array(p, np.float32, copy=True)
+        nz = np.ascontiguousarray(noise, np.float32)
+        self.lib.hmo_dirichlet_mix(_ptr(out), _ptr(nz), out.size, epsilon)
+        return out
+
+    def discrete_pick(self, p, u: float) -> int:
+        a = np.ascontiguousarray(p, np.float32)
+        return int(self.lib.hmo_discrete_pick_f32(_ptr(a), a.size, u))
+
+    def sample_joint(self, pos1, moves_a, p_a, cap_a, moves_b, p_b, cap_b, u3):
+        """-> (status, pick_a, pick_b) for ONE packed position."""
+        pos1 = np.ascontiguousarray(pos1)
+        ma, mb = np.ascontiguousarray(moves_a, np.uint32), np.ascontiguousarray(moves_b, np.uint32)
+        pa, pb = np.ascontiguousarray(p_a, np.float32), np.ascontiguousarray(p_b, np.float32)
+        ca, cb = np.ascontiguousarray(cap_a, np.uint8), np.ascontiguousarray(cap_b, np.uint8)
+        u = np.ascontiguousarray(u3, np.float64)
+        ia, ib = C.c_uint32(), C.c_uint32()
+        st = self.lib.hmo_sample_joint(_ptr(pos1), _ptr(ma), _ptr(pa), _ptr(ca), ma.size, _ptr(mb), _ptr(pb), _ptr(cb),
+                                       mb.size, _ptr(u), C.byref(ia), C.byref(ib))
+        return int(st), int(ia.value), int(ib.value)
+
+    def canonical(self, seed: int, n: int) -> np.ndarray:
+        out = np.zeros(n, np.float64)
+        self.lib.hmo_mt19937_64_canonical(seed, n, _ptr(out))
+        return out
 
     def encode_planes(self, pos: np.ndarray, dtype: str = "f32") -> np.ndarray:
         pos = np.ascontiguousarray(pos)
@@ -203,7 +243,46 @@ class Ref:
         L.hmref_time_planes_f16.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int]
         L.hmref_time_priors_f16.restype = C.c_double
         L.hmref_time_priors_f16.argtypes = [C.POINTER(vp), C.c_int, vp, C.c_int, C.c_int]
+        L.hmref_board_is_capture.argtypes = [vp, C.c_int, C.c_uint32]
+        L.hmref_canonical.argtypes = [C.c_uint64, C.c_int, vp]
+        L.hmref_apply_temperature.argtypes = [vp, C.c_int, C.c_double]
+        L.hmref_sample_joint.argtypes = [vp, vp, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int,
+                                         C.c_uint64, vp, vp, vp]
+        L.hmref_dirichlet_noise.argtypes = [C.c_uint64, C.c_float, C.c_int, vp]
+        L.hmref_dirichlet_mix.argtypes = [vp, vp, C.c_int, C.c_float]
         L.hmref_init()
+
+    # -- root policy stages ---------------------------------------------------------
+    def canonical(self, seed: int, n: int) -> np.ndarray:
+        out = np.zeros(n, np.float64)
+        self.lib.hmref_canonical(seed, n, _ptr(out))
+        return out
+
+    def apply_temperature(self, p, temperature: float) -> np.ndarray:
+        out = np.array(p, np.float32, copy=True)
+        self.lib.hmref_apply_temperature(_ptr(out), out.size, temperature)
+        return out
+
+    def sample_joint(self, moves_a, p_a, cap_a, moves_b, p_b, cap_b, a_on, b_on, tadv, seed):
+        """-> (rc, pick_a, pick_b, draws) from the reference's JointActionCandidate + std::discrete_distribution."""
+        ma, mb = np.ascontiguousarray(moves_a, np.uint32), np.ascontiguousarray(moves_b, np.uint32)
+        pa, pb = np.ascontiguousarray(p_a, np.float32), np.ascontiguousarray(p_b, np.float32)
+        ca, cb = np.ascontiguousarray(cap_a, np.uint8), np.ascontiguousarray(cap_b, np.uint8)
+        ia, ib, dr = C.c_uint32(), C.c_uint32(), C.c_int()
+        rc = self.lib.hmref_sample_joint(_ptr(ma), _ptr(pa), _ptr(ca), ma.size, _ptr(mb), _ptr(pb), _ptr(cb), mb.size,
+                                         int(a_on), int(b_on), int(tadv), seed, C.byref(ia), C.byref(ib), C.byref(dr))
+        return int(rc), int(ia.value), int(ib.value), int(dr.value)
+
+    def dirichlet_noise(self, key: int, alpha: float, n: int) -> np.ndarray:
+        out = np.zeros(n, np.float32)
+        self.lib.hmref_dirichlet_noise(key, alpha, n, _ptr(out))
+        return out
+
+    def dirichlet_mix(self, p, noise, epsilon: float) -> np.ndarray:
+        out = np.array(p, np.float32, copy=True)
+        nz = np.ascontiguousarray(noise, np.float32)
+        self.lib.hmref_dirichlet_mix(_ptr(out), _ptr(nz), out.size, epsilon)
+        return out
 
     # -- boards -------------------------------------------------------------------
     def board(self):
@@ -295,6 +374,9 @@ class RefBoard:
         buf = np.empty(1024, np.uint32)
         k = self.L.hmref_board_legal(self.h, bn, _ptr(buf), 1024)
         return buf[:k].copy()
+
+    def is_capture(self, bn, move) -> int:
+        return int(self.L.hmref_board_is_capture(self.h, bn, int(move)))
 
     def search_actions(self, bn, team_black):
         buf = np.empty(1024, np.uint32)

@@ -32,6 +32,7 @@
 #include "common/utils.h"
 #include "environment/board.h"
 #include "environment/constants.h"
+#include "environment/joint_action.h"
 #include "environment/planes.h"
 #include "Fairy-Stockfish/src/bitboard.h"
 #include "Fairy-Stockfish/src/piece.h"
@@ -310,6 +311,108 @@ double hmref_time_priors_f16(void** boards, int n, const uint16_t* policy, int r
     }
     for (auto& th : pool) th.join();
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// ---- root policy stages ------------------------------------------------
+int hmref_board_is_capture(void* h, int bn, uint32_t m) {
+    return m != 0u && B(h)->is_capture(bn, Stockfish::Move(m)) ? 1 : 0;
+}
+
+// std::generate_canonical<double,53> draws of std::mt19937_64(seed): what std::discrete_distribution
+// consumes in sample_raw_policy_action (selfplay.cc:363-365,389-390).
+void hmref_canonical(uint64_t seed, int n, double* out) {
+    std::mt19937_64 e(seed);
+    for (int i = 0; i < n; ++i) out[i] = std::generate_canonical<double, 53>(e);
+}
+
+// tools/selfplay.cc:167-185 apply_temperature lives in an anonymous namespace of a TU that includes
+// nn/engine.h (NvInfer.h, absent): restated here statement by statement with the same std:: calls.
+int hmref_apply_temperature(float* p, int n, double temperature) {
+    if (n <= 0 || temperature <= 0.0) return 0;
+    const double exponent = 1.0 / temperature;
+    double total = 0.0;
+    for (int i = 0; i < n; ++i) {
+        p[i] = static_cast<float>(std::pow(std::max(0.0f, p[i]), exponent));
+        total += p[i];
+    }
+    if (!std::isfinite(total) || total <= 0.0) {
+        std::fill(p, p + n, 1.0f / static_cast<float>(n));
+        return 1;
+    }
+    for (int i = 0; i < n; ++i) p[i] = static_cast<float>(p[i] / total);
+    return 1;
+}
+
+// The sampling half of sample_raw_policy_action (selfplay.cc:349-392) run on the reference's OWN
+// JointActionCandidate / JointActionRules (environment/joint_action.h) with the real
+// std::discrete_distribution and a std::mt19937_64(seed).  Returns 0 ok, 1 resampled, -3 no legal
+// joint action; *draws = how many canonical doubles the engine handed out.
+int hmref_sample_joint(const uint32_t* mA, const float* pA, const uint8_t* cA, int nA, const uint32_t* mB,
+                       const float* pB, const uint8_t* cB, int nB, int aOnTurn, int bOnTurn, int tadv,
+                       uint64_t seed, uint32_t* iA_out, uint32_t* iB_out, int* draws) {
+    std::mt19937_64 randomEngine(seed);
+    std::vector<Stockfish::Move> actionsA(nA), actionsB(nB);
+    for (int i = 0; i < nA; ++i) actionsA[i] = Stockfish::Move(mA[i]);
+    for (int i = 0; i < nB; ++i) actionsB[i] = Stockfish::Move(mB[i]);
+    std::vector<float> probabilitiesA(pA, pA + nA), probabilitiesB(pB, pB + nB);
+    JointActionRules rules;
+    rules.boardAOnTurn = aOnTurn != 0;
+    rules.boardBOnTurn = bOnTurn != 0;
+    rules.teamHasTimeAdvantage = tadv != 0;
+    rules.boardACanMove = rules.boardAOnTurn && actionsA.size() > 1;
+    rules.boardBCanMove = rules.boardBOnTurn && actionsB.size() > 1;
+    auto make_candidate = [&](size_t iA, size_t iB) {
+        return JointActionCandidate(actionsA[iA], probabilitiesA[iA], iA, actionsB[iB], probabilitiesB[iB], iB, rules,
+                                    cA[iA] != 0, cB[iB] != 0);
+    };
+    int used = (nA >= 2) + (nB >= 2);
+    std::discrete_distribution<size_t> sampleA(probabilitiesA.begin(), probabilitiesA.end());
+    std::discrete_distribution<size_t> sampleB(probabilitiesB.begin(), probabilitiesB.end());
+    // the reference's literal expression (selfplay.cc:365): the two draws are function arguments, so
+    // their order is the compiler's choice (g++ evaluates right to left: B draws first)
+    JointActionCandidate candidate = make_candidate(sampleA(randomEngine), sampleB(randomEngine));
+    int rc = 0;
+    if (candidate.jointPrior < 0.0f) {
+        std::vector<std::pair<size_t, size_t>> legalPairs;
+        std::vector<double> weights;
+        for (size_t iA = 0; iA < actionsA.size(); ++iA)
+            for (size_t iB = 0; iB < actionsB.size(); ++iB) {
+                if (make_candidate(iA, iB).jointPrior < 0.0f) continue;
+                legalPairs.emplace_back(iA, iB);
+                weights.push_back(static_cast<double>(probabilitiesA[iA]) * static_cast<double>(probabilitiesB[iB]));
+            }
+        if (std::accumulate(weights.begin(), weights.end(), 0.0) <= 0.0) {
+            *draws = used;
+            return -3;
+        }
+        std::discrete_distribution<size_t> legalSample(weights.begin(), weights.end());
+        used += weights.size() >= 2;
+        const auto [indexA, indexB] = legalPairs[legalSample(randomEngine)];
+        candidate = make_candidate(indexA, indexB);
+        rc = 1;
+    }
+    *iA_out = static_cast<uint32_t>(candidate.idxA);
+    *iB_out = static_cast<uint32_t>(candidate.idxB);
+    *draws = used;
+    return rc;
+}
+
+// node.h:291-312 applyNoise with the real std::gamma_distribution<float> on std::mt19937_64(key):
+// the reference's noise stream (ours is counter-based: compared in distribution only).
+void hmref_dirichlet_noise(uint64_t key, float alpha, int n, float* noise_out) {
+    std::mt19937_64 randomEngine(key);
+    std::gamma_distribution<float> gamma(alpha, 1.0f);
+    for (int i = 0; i < n; ++i) noise_out[i] = gamma(randomEngine);
+}
+// the mix of node.h:299-311 compiled with the reference's flags
+void hmref_dirichlet_mix(float* priors, const float* noise, int n, float epsilonIn) {
+    if (n <= 1) return;
+    float total = 0.0f;
+    for (int i = 0; i < n; ++i) total += noise[i];
+    if (total <= 0.0f) return;
+    const float epsilon = std::clamp(epsilonIn, 0.0f, 1.0f);
+    for (int index = 0; index < n; ++index)
+        priors[index] = (1.0f - epsilon) * priors[index] + epsilon * noise[index] / total;
 }
 
 int hmref_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }
