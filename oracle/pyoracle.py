@@ -250,7 +250,27 @@ class Ref:
                                          C.c_uint64, vp, vp, vp]
         L.hmref_dirichlet_noise.argtypes = [C.c_uint64, C.c_float, C.c_int, vp]
         L.hmref_dirichlet_mix.argtypes = [vp, vp, C.c_int, C.c_float]
+        L.hmref_product_pack.argtypes = [vp, C.c_int, C.c_int, vp]
+        L.hmref_product_actions.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_int]
+        L.hmref_leafbatch_run.argtypes = [C.c_int, vp, C.c_size_t, C.POINTER(vp), C.c_int, vp] + [vp] * 7 + [C.c_int]
         L.hmref_init()
+
+    # -- the product's include/hm_batch.hpp instantiated on the reference Board ----------
+    def leafbatch_run(self, boards, blob: bytes, root=None, device: int = 0):
+        """LeafBatch.add/submit/collect through the C++ Engine shim -> dict, or a negative error code."""
+        n = len(boards)
+        cap = n * 2 * 256
+        moves, caps = np.zeros(cap, np.uint32), np.zeros(cap, np.uint8)
+        offsets, priors = np.zeros(2 * n + 1, np.uint32), np.zeros(cap, np.float32)
+        values, picks, status = np.zeros(n, np.float32), np.zeros((n, 2), np.uint32), np.zeros(n, np.int32)
+        buf = C.create_string_buffer(blob, len(blob))
+        rc = self.lib.hmref_leafbatch_run(device, buf, len(blob), self.handles(boards), n,
+                                          C.byref(root) if root is not None else None, _ptr(moves), _ptr(caps),
+                                          _ptr(offsets), _ptr(priors), _ptr(values), _ptr(picks), _ptr(status), cap)
+        if rc < 0:
+            return rc
+        return {"moves": moves[:rc], "captures": caps[:rc], "offsets": offsets, "priors": priors[:rc], "values": values,
+                "picks": picks, "status": status}
 
     # -- root policy stages ---------------------------------------------------------
     def canonical(self, seed: int, n: int) -> np.ndarray:
@@ -374,6 +394,18 @@ class RefBoard:
         buf = np.empty(1024, np.uint32)
         k = self.L.hmref_board_legal(self.h, bn, _ptr(buf), 1024)
         return buf[:k].copy()
+
+    def product_pack(self, team_black: int, tadv: int):
+        """hm::pack_position of include/hm_batch.hpp on this reference Board."""
+        out = np.zeros(1, POS_DTYPE)
+        self.L.hmref_product_pack(self.h, int(team_black), int(tadv), _ptr(out))
+        return out
+
+    def product_actions(self, bn, team_black):
+        """hm::append_actions of include/hm_batch.hpp -> (moves, capture flags)."""
+        m, c = np.empty(1024, np.uint32), np.empty(1024, np.uint8)
+        k = self.L.hmref_product_actions(self.h, bn, int(team_black), _ptr(m), _ptr(c), 1024)
+        return m[:k].copy(), c[:k].copy()
 
     def is_capture(self, bn, move) -> int:
         return int(self.L.hmref_board_is_capture(self.h, bn, int(move)))
