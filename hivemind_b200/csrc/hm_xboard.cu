@@ -10,6 +10,7 @@
 // 64x71 attention core.
 #include <cuda_fp16.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "hm_kernels.h"
 
@@ -267,6 +268,178 @@ cross_attention_kernel(const act_t* __restrict__ q, const act_t* __restrict__ kv
     }
 }
 
+// ---- X4 on the tensor cores (warp-level mma.sync m16n8k16, fp32 accumulate) --------------------------
+// The same computation as cross_attention_kernel with the two small GEMMs of a head — S = Q K^T
+// (64 x 80 x 32) and O = P V (64 x 32 x 80) — on mma.sync; the op is HBM-bound (q 24 KB + kv 48 KB in,
+// 24 KB out per (position, board): 98 KB -> 0.03 ms at B = 1024), the tensor instructions only have to
+// get the 3.5 MFLOP per CTA out of the way of the loads.  Everything stays in the channel-major token
+// layout ([channel][square]): Q^T and K^T tiles are read with ldmatrix.trans, V tiles with plain
+// ldmatrix, the probabilities go from the S accumulators straight into the A fragments of the PV
+// product (fp16/bf16, values in [0,1]), and O is staged through the warp's own (dead) Q tile so the
+// global store is 16-byte coalesced.  Keys 64..70 are the 7 context tokens (fp32 ckv rounded to the
+// 16-bit type), 71..79 zero padding masked out of the softmax.
+// CTA = (position, board), 12 warps: warp = (head, half of the 64 queries) = two m16 tiles.
+constexpr int XKEYS = 80;                 // 64 + 7 context + 9 padding
+constexpr int XKP = 88;                   // K/V row pitch in elements (176 B: ldmatrix conflict-free)
+constexpr int XQP = 72;                   // Q row pitch (144 B)
+constexpr int XATT2_SMEM = (384 * XKP + XD * XQP) * 2;
+
+#ifdef HM_ACT_BF16
+#define HM_MMA_16816 "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32"
+#else
+#define HM_MMA_16816 "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32"
+#endif
+__device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile(HM_MMA_16816 " {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void* p) {
+    const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
+    const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a));
+}
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst));
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
+}
+
+__global__ void __launch_bounds__(384, 2)
+cross_attention_mma_kernel(const act_t* __restrict__ q, const act_t* __restrict__ kv,
+                           const float* __restrict__ ckv, act_t* __restrict__ att) {
+    extern __shared__ __align__(16) unsigned char xraw[];
+    act_t* s_kv = reinterpret_cast<act_t*>(xraw);   // [384][XKP]: K rows 0..191, V rows 192..383; cols = keys
+    act_t* s_q = s_kv + 384 * XKP;                  // [192][XQP]: Q^T, later the O^T staging
+    const int n2 = blockIdx.x, pos = n2 >> 1, other = n2 ^ 1;
+    const int tid = threadIdx.x;
+    {
+        const act_t* gkv = kv + static_cast<size_t>(other) * 384 * 64;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int i = tid + 384 * j, row = i >> 3, c = i & 7;
+            cp_async16(s_kv + row * XKP + c * 8, gkv + row * 64 + c * 8);
+        }
+        const act_t* gq = q + static_cast<size_t>(n2) * XD * 64;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int i = tid + 384 * j, row = i >> 3, c = i & 7;
+            cp_async16(s_q + row * XQP + c * 8, gq + row * 64 + c * 8);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        // context keys 64..70 and zero padding 71..79 of row `tid` (K row or V row: ckv holds K | V)
+        const float* c = ckv + static_cast<size_t>(pos) * XCTX * 384 + tid;
+        act_t* dst = s_kv + tid * XKP + 64;
+#pragma unroll
+        for (int t = 0; t < XCTX; ++t) dst[t] = float_to_act(c[t * 384]);
+#pragma unroll
+        for (int t = XCTX; t < XKEYS - 64; ++t) dst[t] = float_to_act(0.0f);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int warp = tid >> 5, lane = tid & 31;
+    const int h = warp >> 1;
+    const int g = lane >> 2, t4 = lane & 3;
+    const int lm = lane >> 3, lr = lane & 7;          // ldmatrix: matrix index, row within it
+    const act_t* kh = s_kv + (h * XDH) * XKP;         // K^T rows of this head: [dim][key]
+    const act_t* vh = s_kv + (XD + h * XDH) * XKP;    // V^T rows: [dim][key]
+    act_t* qh = s_q + (h * XDH) * XQP;                // Q^T rows: [dim][query]
+    const float scale = 0.17677669529663689f;         // 1/sqrt(32)
+
+#pragma unroll 1
+    for (int mt = 0; mt < 2; ++mt) {
+        const int m0 = ((warp & 1) * 2 + mt) * 16;
+        // ---- S = Q K^T : 10 n-tiles of 8 keys, 2 k-steps of 16 dims ----
+        float sacc[10][4];
+#pragma unroll
+        for (int n = 0; n < 10; ++n) sacc[n][0] = sacc[n][1] = sacc[n][2] = sacc[n][3] = 0.0f;
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks) {
+            uint32_t a[4];
+            // matrices: (m 0-7,k 0-7) (m 8-15,k 0-7) (m 0-7,k 8-15) (m 8-15,k 8-15); stored rows = k (dim)
+            ldsm_x4_t(a, qh + (ks * 16 + (lm >> 1) * 8 + lr) * XQP + m0 + (lm & 1) * 8);
+#pragma unroll
+            for (int np = 0; np < 5; ++np) {
+                uint32_t b[4];
+                // matrices: (k 0-7,n 0-7) (k 8-15,n 0-7) (k 0-7,n 8-15) (k 8-15,n 8-15); stored rows = k (dim)
+                ldsm_x4_t(b, kh + (ks * 16 + (lm & 1) * 8 + lr) * XKP + np * 16 + (lm >> 1) * 8);
+                mma16816(sacc[2 * np], a, b[0], b[1]);
+                mma16816(sacc[2 * np + 1], a, b[2], b[3]);
+            }
+        }
+        // ---- softmax over the 71 real keys; rows g (regs 0,1) and g+8 (regs 2,3) ----
+        if (t4 == 3) sacc[8][1] = sacc[8][3] = -INFINITY;   // key 71
+#pragma unroll
+        for (int r = 0; r < 4; ++r) sacc[9][r] = -INFINITY;  // keys 72..79
+        float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+        for (int n = 0; n < 10; ++n) {
+            mx0 = fmaxf(mx0, fmaxf(sacc[n][0], sacc[n][1]));
+            mx1 = fmaxf(mx1, fmaxf(sacc[n][2], sacc[n][3]));
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        float sum0 = 0.0f, sum1 = 0.0f;
+        uint32_t pfr[10][2];
+#pragma unroll
+        for (int n = 0; n < 10; ++n) {
+            const float e0 = __expf((sacc[n][0] - mx0) * scale), e1 = __expf((sacc[n][1] - mx0) * scale);
+            const float e2 = __expf((sacc[n][2] - mx1) * scale), e3 = __expf((sacc[n][3] - mx1) * scale);
+            sum0 += e0 + e1;
+            sum1 += e2 + e3;
+            pfr[n][0] = pack_act2(e0, e1);
+            pfr[n][1] = pack_act2(e2, e3);
+        }
+        sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1);
+        sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+        sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1);
+        sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+        // ---- O = P V : 4 n-tiles of 8 dims, 5 k-steps of 16 keys ----
+        float oacc[4][4];
+#pragma unroll
+        for (int n = 0; n < 4; ++n) oacc[n][0] = oacc[n][1] = oacc[n][2] = oacc[n][3] = 0.0f;
+#pragma unroll
+        for (int ks = 0; ks < 5; ++ks) {
+            const uint32_t a[4] = {pfr[2 * ks][0], pfr[2 * ks][1], pfr[2 * ks + 1][0], pfr[2 * ks + 1][1]};
+#pragma unroll
+            for (int np = 0; np < 2; ++np) {
+                uint32_t b[4];
+                // matrices: (n 0-7,k 0-7) (n 0-7,k 8-15) (n 8-15,k 0-7) (n 8-15,k 8-15); stored rows = n (dim)
+                ldsm_x4(b, vh + (np * 16 + (lm >> 1) * 8 + lr) * XKP + ks * 16 + (lm & 1) * 8);
+                mma16816(oacc[2 * np], a, b[0], b[1]);
+                mma16816(oacc[2 * np + 1], a, b[2], b[3]);
+            }
+        }
+        // ---- O^T into the warp's own Q tile (all its Q fragments are consumed) ----
+        const float inv0 = 1.0f / sum0, inv1 = 1.0f / sum1;
+        __syncwarp();
+#pragma unroll
+        for (int n = 0; n < 4; ++n) {
+            act_t* o0 = qh + (n * 8 + 2 * t4) * XQP + m0 + g;
+            o0[0] = float_to_act(oacc[n][0] * inv0);
+            o0[XQP] = float_to_act(oacc[n][1] * inv0);
+            o0[8] = float_to_act(oacc[n][2] * inv1);
+            o0[XQP + 8] = float_to_act(oacc[n][3] * inv1);
+        }
+    }
+    __syncthreads();
+    {
+        act_t* gout = att + static_cast<size_t>(n2) * XD * 64;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int i = tid + 384 * j, row = i >> 3, c = i & 7;
+            *reinterpret_cast<uint4*>(gout + row * 64 + c * 8) = *reinterpret_cast<const uint4*>(s_q + row * XQP + c * 8);
+        }
+    }
+}
+
 // ---- launchers ---------------------------------------------------------------------------
 void launch_token_embed(const float* pre, const act_t* planes, const float* wp, const float* bias,
                         const float* pos_emb, const float* board_emb, act_t* tok, int n, cudaStream_t s) {
@@ -287,11 +460,17 @@ void launch_context_kv(const float* ctx, const float* g, const float* b, const f
 }
 bool xboard_prepare() {
     return cudaFuncSetAttribute(cross_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                XATT_SMEM) == cudaSuccess;
+                                XATT_SMEM) == cudaSuccess &&
+           cudaFuncSetAttribute(cross_attention_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                XATT2_SMEM) == cudaSuccess;
 }
 void launch_cross_attention(const act_t* q, const act_t* kv, const float* ckv, act_t* att, int n,
                             cudaStream_t s) {
-    if (n > 0) cross_attention_kernel<<<2 * n, 384, XATT_SMEM, s>>>(q, kv, ckv, att);
+    if (n <= 0) return;
+    // HM_XATT_FP32=1 selects the CUDA-core fp32 kernel (bring-up / numerical comparison)
+    static const bool fp32_path = getenv("HM_XATT_FP32") != nullptr;
+    if (fp32_path) cross_attention_kernel<<<2 * n, 384, XATT_SMEM, s>>>(q, kv, ckv, att);
+    else cross_attention_mma_kernel<<<2 * n, 384, XATT2_SMEM, s>>>(q, kv, ckv, att);
 }
 
 }  // namespace hm
