@@ -730,7 +730,7 @@ static bool setup_worker(Engine* e, Worker& w) {
     auto& ops = w.ops_trunk;
     if (!add_dense(ops, net.stem, w.d_planes, HM_NB_INPUT_CHANNELS, B, w.d_trunk, true, false)) return false;
     int nblk = static_cast<int>(net.blocks.size());
-    if (const char* stop = getenv("HM_TRUNK_STOP"))  // debugging aid (tools/diagnose.py): truncate the trunk
+    if (const char* stop = getenv("HM_TRUNK_STOP"))  // debugging aid (tests/diag/diagnose.py): truncate the trunk
         nblk = std::max(0, std::min(nblk, atoi(stop)));
     // the whole trunk is ONE launch: ECA gates are computed inside the kernel (a gate depends on the
     // channel means of the SAME position only, builder_util.py:77-80)

@@ -27,38 +27,63 @@ constexpr float LN_EPS = 1e-5f;
 // tok[pos][b][o][sq] = relu(pre + bias[b][o] + sum_c wp[b][o][c] * planes[pos][37b + c][sq])
 //                      + pos_emb_t[o][sq] + board_emb[b][o]        (rise_mobile_v3.py:374-385;
 //                      pos_emb_t = the position embedding transposed to channel-major at load)
-// grid (n, 2), 256 threads = 4 channel groups x 64 squares.
+// grid (ceil(n / TE_POS), 2), 256 threads = 4 channel groups x 64 squares; a CTA stages the board's
+// 192 x 37 plane weights in shared memory once and walks TE_POS positions with them.
+constexpr int TE_POS = 4;
 __global__ void __launch_bounds__(256)
 token_embed_kernel(const float* __restrict__ pre, const act_t* __restrict__ planes,
                    const float* __restrict__ wp, const float* __restrict__ bias,
                    const float* __restrict__ pos_emb, const float* __restrict__ board_emb,
-                   act_t* __restrict__ tok) {
+                   act_t* __restrict__ tok, int n) {
     __shared__ __align__(16) float s_wp[XD * 40];   // rows padded 37 -> 40 for 16-byte broadcast reads
-    const int pos = blockIdx.x, b = blockIdx.y;
+    __shared__ float s_add[XD];                     // bias (before the ReLU)
+    __shared__ float s_emb[XD];                     // board embedding (after it)
+    const int b = blockIdx.y;
     for (int i = threadIdx.x; i < XD * 40; i += 256) {
         const int o = i / 40, c = i - o * 40;
         s_wp[i] = c < 37 ? wp[(b * XD + o) * 37 + c] : 0.0f;
     }
+    if (threadIdx.x < XD) {
+        s_add[threadIdx.x] = bias[b * XD + threadIdx.x];
+        s_emb[threadIdx.x] = board_emb[b * XD + threadIdx.x];
+    }
     const int sq = threadIdx.x & 63, grp = threadIdx.x >> 6;
-    float pl[40];
-#pragma unroll
-    for (int c = 0; c < 37; ++c)
-        pl[c] = act_to_float(planes[(static_cast<size_t>(pos) * 74 + 37 * b + c) * 64 + sq]);
-    pl[37] = pl[38] = pl[39] = 0.0f;
     __syncthreads();
-    for (int o = grp * 48; o < grp * 48 + 48; ++o) {
-        float v = pre[(static_cast<size_t>(pos) * 384 + b * XD + o) * 64 + sq] + bias[b * XD + o];
-        const float4* w = reinterpret_cast<const float4*>(s_wp + o * 40);
+    for (int pp = 0; pp < TE_POS; ++pp) {
+        const int pos = blockIdx.x * TE_POS + pp;
+        if (pos >= n) break;
+        float pl[40];
 #pragma unroll
-        for (int c4 = 0; c4 < 10; ++c4) {
-            const float4 ww = w[c4];
-            v = fmaf(ww.x, pl[4 * c4], v);
-            v = fmaf(ww.y, pl[4 * c4 + 1], v);
-            v = fmaf(ww.z, pl[4 * c4 + 2], v);
-            v = fmaf(ww.w, pl[4 * c4 + 3], v);
+        for (int c = 0; c < 37; ++c)
+            pl[c] = act_to_float(planes[(static_cast<size_t>(pos) * 74 + 37 * b + c) * 64 + sq]);
+        pl[37] = pl[38] = pl[39] = 0.0f;
+        const float* prow = pre + (static_cast<size_t>(pos) * 384 + b * XD) * 64 + sq;
+        act_t* trow = tok + (static_cast<size_t>(pos) * 384 + b * XD) * 64 + sq;
+        // 8 outputs per step: their `pre` / embedding loads are issued together, then the FMAs
+#pragma unroll 1
+        for (int o0 = grp * 48; o0 < grp * 48 + 48; o0 += 8) {
+            float v[8], e[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                v[j] = prow[(o0 + j) * 64];
+                e[j] = pos_emb[(o0 + j) * 64 + sq];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int o = o0 + j;
+                float a = v[j] + s_add[o];
+                const float4* w = reinterpret_cast<const float4*>(s_wp + o * 40);
+#pragma unroll
+                for (int c4 = 0; c4 < 10; ++c4) {
+                    const float4 ww = w[c4];
+                    a = fmaf(ww.x, pl[4 * c4], a);
+                    a = fmaf(ww.y, pl[4 * c4 + 1], a);
+                    a = fmaf(ww.z, pl[4 * c4 + 2], a);
+                    a = fmaf(ww.w, pl[4 * c4 + 3], a);
+                }
+                trow[o * 64] = float_to_act(fmaxf(a, 0.0f) + e[j] + s_emb[o]);
+            }
         }
-        v = fmaxf(v, 0.0f) + pos_emb[o * 64 + sq] + board_emb[b * XD + o];
-        tok[(static_cast<size_t>(pos) * 384 + b * XD + o) * 64 + sq] = float_to_act(v);
     }
 }
 
@@ -443,7 +468,7 @@ cross_attention_mma_kernel(const act_t* __restrict__ q, const act_t* __restrict_
 // ---- launchers ---------------------------------------------------------------------------
 void launch_token_embed(const float* pre, const act_t* planes, const float* wp, const float* bias,
                         const float* pos_emb, const float* board_emb, act_t* tok, int n, cudaStream_t s) {
-    if (n > 0) token_embed_kernel<<<dim3(n, 2), 256, 0, s>>>(pre, planes, wp, bias, pos_emb, board_emb, tok);
+    if (n > 0) token_embed_kernel<<<dim3((n + TE_POS - 1) / TE_POS, 2), 256, 0, s>>>(pre, planes, wp, bias, pos_emb, board_emb, tok, n);
 }
 void launch_context_tokens(const act_t* planes, const float* pocket_w, const float* pocket_b,
                            const float* scalar_w, const float* scalar_b, const float* role, float* ctx,

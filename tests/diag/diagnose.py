@@ -3,7 +3,7 @@
 Compares every inspectable activation of the CUDA path with the fp32 oracle, first on a
 truncated network, then on the full network.  HM_TRUNK_STOP=k in the environment stops the trunk
 after block k-1 (0 = stem only) so the intermediate activation is inspectable.
-Usage:  python tools/diagnose.py [n_blocks ...]
+Usage:  python tests/diag/diagnose.py [n_blocks ...]
 """
 import os
 import sys
@@ -11,7 +11,7 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 

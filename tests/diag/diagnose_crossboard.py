@@ -1,14 +1,14 @@
 """Stage-by-stage check of the crossboard-risev33 CUDA path against the fp32 oracle (verbose).
-Usage:  python tools/diagnose_crossboard.py [n_positions]"""
+Usage:  python tests/diag/diagnose_crossboard.py [n_positions]"""
 import os
 import sys
 import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tools"))
+sys.path.insert(0, os.path.join(ROOT, "tests", "diag"))
 
 from diagnose import stats  # noqa: E402
 from hivemind_b200 import weights as W  # noqa: E402

@@ -221,7 +221,7 @@ def test_crossboard_fused_path_matches_reference_model(cross_engine, gold_positi
     # <= 2e-3.  The random-init crossboard heads amplify trunk perturbations more than the risev33
     # heads do: rounding ONLY the trunk weights to fp16 (what the reference's own fp16 TensorRT
     # plan does as well) already moves the fp32 model's value by 8e-3 on these positions, our
-    # heads add 2e-3 (tools/diagnose_crossboard.py, DESIGN.md "Precision").  Policy stays far
+    # heads add 2e-3 (tests/diag/diagnose_crossboard.py, DESIGN.md "Precision").  Policy stays far
     # inside its bar (KL 3e-4 vs 1e-3).
     dv = np.abs(raw[:, 0] - f["value"])
     assert dv.max() <= 2e-2 and dv.mean() <= 2e-3
