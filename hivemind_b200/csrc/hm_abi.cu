@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <functional>
 #include <mutex>
 
 #include "hm_kernels.h"
@@ -546,6 +547,64 @@ int hm_engine_bench_resident_multi(hm_engine* h, int n_workers, int iters, float
     if (launches_per_pass)
         *launches_per_pass = static_cast<int>(w0->ops_fused_in.size() + w0->ops_trunk.size() + w0->ops_fused_out.size());
     return ok ? 1 : 0;
+    HM_CATCH(0)
+}
+
+static bool time_launches(cudaStream_t s, int iters, const std::function<void()>& launch, float* ms_total) {
+    cudaEvent_t e0, e1;
+    if (!cuda_ok(cudaEventCreate(&e0), "event") || !cuda_ok(cudaEventCreate(&e1), "event")) return false;
+    launch();  // warm-up
+    bool ok = cuda_ok(cudaStreamSynchronize(s), "warm-up") && cuda_ok(cudaEventRecord(e0, s), "record");
+    for (int i = 0; ok && i < iters; ++i) launch();
+    ok = ok && cuda_ok(cudaGetLastError(), "bench kernel") && cuda_ok(cudaEventRecord(e1, s), "record") &&
+         cuda_ok(cudaEventSynchronize(e1), "event sync");
+    float ms = 0.f;
+    if (ok) ok = cuda_ok(cudaEventElapsedTime(&ms, e0, e1), "elapsed");
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (ms_total) *ms_total = ms;
+    return ok;
+}
+
+int hm_bench_planes(hm_engine* h, const hm_packed_pos* pos, size_t n, int dtype, int iters, float* ms_total) {
+    HM_TRY
+    if (!h || !pos || n == 0 || iters <= 0) { set_error("bad argument"); return 0; }
+    if (dtype < HM_DTYPE_F32 || dtype > HM_DTYPE_U8) { set_error("bad dtype"); return 0; }
+    if (!use_device(h)) return 0;
+    std::lock_guard<std::mutex> lock(h->util_mutex);
+    const size_t esz = dtype == HM_DTYPE_F32 ? 4 : dtype == HM_DTYPE_U8 ? 1 : 2;
+    DevBuf<hm_packed_pos> dpos;
+    DevBuf<uint8_t> dout;
+    if (!dpos.alloc(n) || !dout.alloc(n * HM_NB_INPUT_VALUES * esz)) return 0;
+    cudaStream_t s = h->e.util_stream;
+    if (!cuda_ok(cudaMemcpyAsync(dpos.p, pos, n * sizeof(hm_packed_pos), cudaMemcpyHostToDevice, s), "H2D pos")) return 0;
+    return time_launches(s, iters, [&] { launch_planes_nchw(dpos.p, static_cast<int>(n), dout.p, dtype, s); }, ms_total) ? 1 : 0;
+    HM_CATCH(0)
+}
+
+int hm_bench_priors(hm_engine* h, const hm_packed_pos* pos, size_t n_pos, const uint32_t* moves,
+                    const uint32_t* move_offsets, int iters, float* ms_total) {
+    HM_TRY
+    if (!h || !pos || !moves || !move_offsets || n_pos == 0 || iters <= 0) { set_error("bad argument"); return 0; }
+    if (!use_device(h)) return 0;
+    std::lock_guard<std::mutex> lock(h->util_mutex);
+    const size_t n_moves = move_offsets[2 * n_pos];
+    const size_t L = n_pos * 2 * HM_NB_POLICY_VALUES;
+    DevBuf<hm_packed_pos> dpos;
+    DevBuf<uint32_t> dm, doff;
+    DevBuf<float> dp, dl;
+    if (!dpos.alloc(n_pos) || !dm.alloc(n_moves) || !doff.alloc(2 * n_pos + 1) || !dp.alloc(n_moves) || !dl.alloc(L)) return 0;
+    cudaStream_t s = h->e.util_stream;
+    // synthetic logits: a cheap deterministic pattern (the bytes gathered are what is timed, not their values)
+    std::vector<float> row(2 * HM_NB_POLICY_VALUES);
+    for (size_t i = 0; i < row.size(); ++i) row[i] = static_cast<float>(static_cast<int>((i * 7) % 41) - 20) * 0.25f;
+    bool ok = cuda_ok(cudaMemcpyAsync(dpos.p, pos, n_pos * sizeof(hm_packed_pos), cudaMemcpyHostToDevice, s), "H2D") &&
+              cuda_ok(cudaMemcpyAsync(dm.p, moves, n_moves * 4, cudaMemcpyHostToDevice, s), "H2D") &&
+              cuda_ok(cudaMemcpyAsync(doff.p, move_offsets, (2 * n_pos + 1) * 4, cudaMemcpyHostToDevice, s), "H2D");
+    for (size_t p = 0; ok && p < n_pos; ++p)
+        ok = cuda_ok(cudaMemcpyAsync(dl.p + p * row.size(), row.data(), row.size() * 4, cudaMemcpyHostToDevice, s), "H2D logits");
+    if (!ok) return 0;
+    return time_launches(s, iters, [&] { launch_policy_priors_packed(dl.p, dpos.p, static_cast<int>(n_pos), dm.p, doff.p, dp.p, s); }, ms_total) ? 1 : 0;
     HM_CATCH(0)
 }
 

@@ -70,40 +70,56 @@ template <> __device__ __forceinline__ uint8_t cvt_plane<uint8_t>(float v) {
     return static_cast<uint8_t>(lroundf(fminf(fmaxf(v, 0.0f), 1.0f) * 255.0f));
 }
 
-// NCHW [n][74][64]: thread = one (position, channel) plane = 64 consecutive outputs, so a warp
-// writes 32 consecutive planes (a contiguous 32*64*sizeof(T) span) with 16-byte stores, and the
-// 256-byte record is read through the read-only path (each record is shared by 74 threads).
+// NCHW [n][74][64].  A lane works out the (mask, value) of ONE (position, channel) plane — so the table
+// logic runs once per plane — and the warp then writes its 32 planes cooperatively: in step k lane l
+// stores 16-byte piece l % PIECES of plane k*(32/PIECES) + l / PIECES, fetching that plane's mask and
+// value by shuffle, so every store instruction covers 512 CONSECUTIVE bytes (whole 128-byte lines).
+// The 256-byte record is read through the read-only path (each record is shared by 74 lanes).
 constexpr int PL_THREADS = 256;
 template <typename T>
 __global__ void __launch_bounds__(PL_THREADS)
 planes_nchw_kernel(const hm_packed_pos* __restrict__ pos, int n, T* __restrict__ out) {
-    const int item = blockIdx.x * PL_THREADS + threadIdx.x;
-    if (item >= n * HM_NB_INPUT_CHANNELS) return;
-    const int p = item / HM_NB_INPUT_CHANNELS;
-    const int c = item - p * HM_NB_INPUT_CHANNELS;
-    const int bi = c >= HM_NB_CHANNELS_PER_BOARD ? 1 : 0, ch = c - bi * HM_NB_CHANNELS_PER_BOARD;
-    const int flags0 = reinterpret_cast<const uint8_t*>(pos + p)[offsetof(hm_packed_board, flags)];
-    const int team_black = (flags0 & HM_FLAG_TEAM_BLACK) ? 1 : 0;
-    const int tadv = (flags0 & HM_FLAG_TIME_ADVANTAGE) ? 1 : 0;
-    const int first = bi == 0 ? team_black : 1 - team_black;
-    // planes.cc:90-93: board A flipped iff team BLACK, board B iff team WHITE  (== first)
-    const PlaneDesc d = plane_desc(pos[p].board[bi], first, first, tadv, ch);
-    const T on = cvt_plane<T>(d.value);
+    constexpr int PER = 16 / sizeof(T);     // outputs per 16-byte store
+    constexpr int PIECES = 64 / PER;        // stores per plane: 16 (f32), 8 (f16/bf16), 4 (u8)
+    constexpr int PPS = 32 / PIECES;        // planes written per step
+    const long long total = static_cast<long long>(n) * HM_NB_INPUT_CHANNELS;
+    const long long item = static_cast<long long>(blockIdx.x) * PL_THREADS + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    uint64_t mask = 0ull;
+    float value = 0.0f;
+    if (item < total) {
+        const int p = static_cast<int>(item / HM_NB_INPUT_CHANNELS);
+        const int c = static_cast<int>(item - static_cast<long long>(p) * HM_NB_INPUT_CHANNELS);
+        const int bi = c >= HM_NB_CHANNELS_PER_BOARD ? 1 : 0, ch = c - bi * HM_NB_CHANNELS_PER_BOARD;
+        const int flags0 = reinterpret_cast<const uint8_t*>(pos + p)[offsetof(hm_packed_board, flags)];
+        const int team_black = (flags0 & HM_FLAG_TEAM_BLACK) ? 1 : 0;
+        const int tadv = (flags0 & HM_FLAG_TIME_ADVANTAGE) ? 1 : 0;
+        const int first = bi == 0 ? team_black : 1 - team_black;
+        // planes.cc:90-93: board A flipped iff team BLACK, board B iff team WHITE  (== first)
+        const PlaneDesc d = plane_desc(pos[p].board[bi], first, first, tadv, ch);
+        mask = d.mask;
+        value = d.value;
+    }
+    const long long base = item - lane;     // first plane of this warp
     const T off = cvt_plane<T>(0.0f);
-    T* dst = out + static_cast<size_t>(item) * 64;
-    constexpr int PER = 16 / sizeof(T);  // outputs per 16-byte store
+    const int j = lane % PIECES;
 #pragma unroll
-    for (int j = 0; j < 64 / PER; ++j) {
+    for (int k = 0; k < PIECES; ++k) {
+        const int src = k * PPS + lane / PIECES;
+        const uint64_t m = __shfl_sync(0xffffffffu, mask, src);
+        const T on = cvt_plane<T>(__shfl_sync(0xffffffffu, value, src));
+        const uint32_t bits = static_cast<uint32_t>(m >> (j * PER));
         __align__(16) T v[PER];
 #pragma unroll
-        for (int e = 0; e < PER; ++e) v[e] = ((d.mask >> (j * PER + e)) & 1ull) ? on : off;
-        reinterpret_cast<uint4*>(dst)[j] = *reinterpret_cast<const uint4*>(v);
+        for (int e = 0; e < PER; ++e) v[e] = ((bits >> e) & 1u) ? on : off;
+        if (base + src < total)
+            reinterpret_cast<uint4*>(out + (base + src) * 64)[j] = *reinterpret_cast<const uint4*>(v);
     }
 }
 
 void launch_planes_nchw(const hm_packed_pos* pos, int n, void* out, int dtype, cudaStream_t s) {
     if (n <= 0) return;
-    const int grid = (n * HM_NB_INPUT_CHANNELS + PL_THREADS - 1) / PL_THREADS;
+    const unsigned grid = static_cast<unsigned>((static_cast<long long>(n) * HM_NB_INPUT_CHANNELS + PL_THREADS - 1) / PL_THREADS);
     switch (dtype) {
         case HM_DTYPE_F32: planes_nchw_kernel<float><<<grid, PL_THREADS, 0, s>>>(pos, n, static_cast<float*>(out)); break;
         case HM_DTYPE_F16: planes_nchw_kernel<__half><<<grid, PL_THREADS, 0, s>>>(pos, n, static_cast<__half*>(out)); break;

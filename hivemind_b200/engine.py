@@ -260,6 +260,26 @@ class Engine:
             raise RuntimeError(_lib.last_error())
         return ms.value, n.value
 
+    def benchPlanes(self, pos: np.ndarray, dtype: str = "f16", iters: int = 20) -> float:
+        """Device-resident stand-alone plane encode of len(pos) positions -> ms per launch."""
+        pos = np.ascontiguousarray(pos)
+        ms = C.c_float()
+        code = {"f32": _lib.DTYPE_F32, "f16": _lib.DTYPE_F16, "bf16": _lib.DTYPE_BF16, "u8": _lib.DTYPE_U8}[dtype]
+        if not self._L.hm_bench_planes(self._h, pos.ctypes.data, pos.shape[0], code, iters, C.byref(ms)):
+            raise RuntimeError(_lib.last_error())
+        return ms.value / iters
+
+    def benchPriors(self, pos, moves, offsets, iters: int = 20) -> float:
+        """Device-resident stand-alone legal-move gather + softmax -> ms per launch."""
+        pos = np.ascontiguousarray(pos)
+        moves = np.ascontiguousarray(moves, np.uint32)
+        offsets = np.ascontiguousarray(offsets, np.uint32)
+        ms = C.c_float()
+        if not self._L.hm_bench_priors(self._h, pos.ctypes.data, pos.shape[0], moves.ctypes.data, offsets.ctypes.data,
+                                       iters, C.byref(ms)):
+            raise RuntimeError(_lib.last_error())
+        return ms.value / iters
+
     def benchResidentMulti(self, iters: int, numWorkers: int):
         """`iters` fused passes issued round-robin on `numWorkers` worker streams; device ms."""
         ms, n = C.c_float(), C.c_int()

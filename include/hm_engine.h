@@ -246,6 +246,15 @@ int hm_engine_bench_resident(hm_engine* e, size_t worker, int iters, float* ms_t
 int hm_engine_bench_resident_multi(hm_engine* e, int n_workers, int iters, float* ms_total,
                                    int* launches_per_pass);
 
+/* Stand-alone, device-resident timing of the bandwidth stages at sizes where GB/s means something
+ * (the plane encoder is launch-bound at B = 512).  planes: n positions (copied to the
+ * device once) encoded `iters` times into a device buffer of `dtype`; priors: get_normalized_probability
+ * for n_pos positions over synthetic fp32 logits already on the device.  Elapsed CUDA-event
+ * milliseconds for all `iters` launches. */
+int hm_bench_planes(hm_engine* e, const hm_packed_pos* pos, size_t n, int dtype, int iters, float* ms_total);
+int hm_bench_priors(hm_engine* e, const hm_packed_pos* pos, size_t n_pos, const uint32_t* moves,
+                    const uint32_t* move_offsets, int iters, float* ms_total);
+
 /* Per-kernel timing of one pass with CUDA events between launches: fills up to `cap`
  * entries of (name, ms); returns the count in *n. */
 typedef struct hm_kernel_time {

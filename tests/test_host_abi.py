@@ -54,12 +54,14 @@ def test_engine_fails_loudly_without_cuda_device():
 
 
 def test_product_package_never_imports_the_oracle():
-    pkg = os.path.join(ROOT, "hivemind_b200")
-    for base, _, files in os.walk(pkg):
-        for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".h", ".cc")):
-                text = open(os.path.join(base, f), errors="ignore").read()
-                assert "import oracle" not in text and "from oracle" not in text and "oracle/" not in text, f
+    """hivemind_b200/, include/ and tools/ (everything shipped or run outside tests/ and bench.py's CPU legs)
+    never import, include or link anything under oracle/."""
+    for top in ("hivemind_b200", "include", "tools"):
+        for base, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cc", ".sh")):
+                    text = open(os.path.join(base, f), errors="ignore").read()
+                    assert "import oracle" not in text and "from oracle" not in text and "oracle/" not in text, f
 
 
 @pytest.mark.skipif(shutil.which("g++") is None, reason="no g++")
