@@ -55,7 +55,7 @@ def test_reference_selfplay_command_plays_games_and_writes_chunks(model_dir):
     from oracle.chunk_oracle import read_chunk
 
     out = model_dir / "games"
-    nodes, games = 200, 2
+    nodes, games = int(os.environ.get("HM_DROPIN_NODES", "200")), int(os.environ.get("HM_DROPIN_GAMES", "2"))
     t0 = time.time()
     r = subprocess.run([BIN, "selfplay", "--model", "models/model.onnx", "--games", str(games), "--nodes", str(nodes),
                         "--output", str(out), "--seed", "7", "--max-macro-plies", "40", "--chunk-samples", "64"],
