@@ -38,7 +38,12 @@ struct __half {
 #define HM_DEFAULT_WORKERS 4 /* SearchParams::NUM_SEARCH_THREADS, search_params.h:30 */
 #endif
 
-class Engine {
+// The class is called `Engine`, as in the reference, unless a build renames it (the batching build of
+// integration/nn/engine.h gives that name to hm::BatchingEngine instead).
+#ifndef HM_ENGINE_CLASS_NAME
+#define HM_ENGINE_CLASS_NAME Engine
+#endif
+class HM_ENGINE_CLASS_NAME {
 public:
     // engine.h:52-58
     struct HalfInferenceOutputs {
@@ -51,17 +56,17 @@ public:
 
     // engine.h:60 (the reference fixes the worker count at compile time; here it is a
     // constructor argument with the same default)
-    explicit Engine(int deviceId, int batchSize = HM_DEFAULT_BATCH_SIZE,
+    explicit HM_ENGINE_CLASS_NAME(int deviceId, int batchSize = HM_DEFAULT_BATCH_SIZE,
                     int numWorkers = HM_DEFAULT_WORKERS)
         : m_deviceId(deviceId), m_batchSize(batchSize) {
         m_handle = hm_engine_create(deviceId, batchSize, numWorkers);
         if (m_handle == nullptr) report("Engine");
     }
-    ~Engine() {
+    ~HM_ENGINE_CLASS_NAME() {
         if (m_handle != nullptr) hm_engine_destroy(m_handle);
     }
-    Engine(const Engine&) = delete;
-    Engine& operator=(const Engine&) = delete;
+    HM_ENGINE_CLASS_NAME(const HM_ENGINE_CLASS_NAME&) = delete;
+    HM_ENGINE_CLASS_NAME& operator=(const HM_ENGINE_CLASS_NAME&) = delete;
 
     // engine.h:66.  `onnxFile` may name the reference's .onnx: the packed weights are read
     // from the sibling .hvmw written by `python -m hivemind_b200.weights`;

@@ -11,4 +11,16 @@
 #ifndef HM_DEFAULT_WORKERS
 #define HM_DEFAULT_WORKERS SearchParams::NUM_SEARCH_THREADS
 #endif
+#ifndef HM_BATCHING_ENGINE
 #include "hm_engine.hpp"  // class Engine, Engine::HalfInferenceOutputs
+#else
+// Many concurrent games on one evaluator: `Engine` is the small-batch facade that coalesces the requests of
+// all engines of a device into large device batches (include/hm_batching_engine.hpp).  The reference's
+// sources still compile unchanged; integration/multigame_selfplay.cc runs its run_selfplay from many threads.
+#define HM_ENGINE_CLASS_NAME DirectEngine
+#include "hm_batching_engine.hpp"
+class Engine : public hm::BatchingEngine {
+public:
+    using hm::BatchingEngine::BatchingEngine;
+};
+#endif

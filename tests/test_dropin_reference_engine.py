@@ -75,3 +75,36 @@ def test_reference_selfplay_command_plays_games_and_writes_chunks(model_dir):
     assert len(first["x"]) == 4736 and first["search_nodes"] > 0
     print(f"\n[dropin] reference selfplay: {games} games, {samples} searched positions x {nodes} nodes in {dt:.1f}s "
           f"(~{samples * nodes / dt:.0f} search nodes/s incl. start-up; batch 8, the reference's own driver)")
+
+
+MG = os.path.join(ROOT, "oracle", "_ref", "hivemind_multigame")
+
+
+@pytest.mark.skipif(not os.path.exists(MG), reason="oracle/_ref/hivemind_multigame not built (needs /root/reference)")
+@pytest.mark.gpu
+def test_many_concurrent_reference_games_share_one_evaluator(model_dir):
+    """include/hm_batching_engine.hpp: G threads run the reference's unmodified run_selfplay, each with its own
+    small-batch `Engine` facade; their 8-position requests are coalesced into large device batches."""
+    from oracle.chunk_oracle import read_chunk
+
+    g = int(os.environ.get("HM_MG_CONCURRENT", "8"))
+    nodes = int(os.environ.get("HM_MG_NODES", "200"))
+    per = int(os.environ.get("HM_MG_GAMES_PER_THREAD", "1"))
+    out = model_dir / f"mg_{g}_{nodes}"
+    r = subprocess.run(["timeout", "600", MG, "--model", "models/model.onnx", "--concurrent", str(g), "--games-per-thread", str(per),
+                        "--nodes", str(nodes), "--output", str(out), "--seed", "11", "--max-macro-plies", "40"],
+                       cwd=model_dir, capture_output=True, text=True, timeout=700)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    m = re.search(r"multigame summary: concurrent (\d+) games_per_thread (\d+) nodes (\d+) seconds ([0-9.eE+-]+) device_passes (\d+) "
+                  r"rows_served (\d+) large_batch (\d+) failures (\d+)", r.stdout)
+    assert m, r.stdout[-2000:]
+    secs, passes, rows, big, failures = float(m.group(4)), int(m.group(5)), int(m.group(6)), int(m.group(7)), int(m.group(8))
+    assert failures == 0 and passes > 0
+    chunks = [os.path.join(b, f) for b, _, fs in os.walk(out) for f in fs if f.endswith(".hvm")]
+    samples = [s for c in chunks for s in read_chunk(c)]
+    assert len({os.path.dirname(os.path.dirname(c)) for c in chunks}) == g  # every thread finished its games
+    searched = sum(s["search_nodes"] for s in samples)
+    assert searched > 0
+    print(f"\n[multigame] {g} concurrent reference games x {per}, {nodes} nodes/move: {len(samples)} searched positions, "
+          f"{searched} search nodes in {secs:.2f}s = {searched / secs:.0f} nodes/s; {passes} device passes of {big} rows, "
+          f"{rows / passes:.1f} live rows per pass ({rows / secs:.0f} evaluated positions/s)")
