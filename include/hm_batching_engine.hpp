@@ -74,6 +74,7 @@ public:
     bool enqueue(int slot, const uint16_t* obs) {
         Group& g = m_groups[slot % kGroups];
         const int local = slot / kGroups;
+        if (!m_engine || !g.staging) return false;     // no CUDA device: there is no CPU fallback
         {
             std::lock_guard<std::mutex> lock(g.mutex);
             if (g.state[local] != IDLE) return false;  // one request in flight per worker (engine.cc:579-588)

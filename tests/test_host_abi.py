@@ -187,3 +187,43 @@ def test_checkpoint_conversion_cli(tmp_path):
     torch.save({k: torch.from_numpy(v) for k, v in sd.items()}, ck)
     with pytest.raises(KeyError):
         W.convert_checkpoint(str(ck), str(out))
+
+
+@pytest.mark.skipif(shutil.which("g++") is None, reason="no g++")
+def test_batching_engine_header_compiles_alone_and_fails_loudly_without_gpu(tmp_path):
+    """include/hm_batching_engine.hpp needs nothing of the reference; without a CUDA device loadNetwork and the
+    request path return false (no CPU fallback, no hang)."""
+    import torch
+
+    from hivemind_b200 import build as hb
+
+    lib = hb.build()
+    src = tmp_path / "b.cc"
+    src.write_text(r'''
+#include <cstdio>
+#include <vector>
+#include "hm_batching_engine.hpp"
+int main() {
+    hm::BatchingEngine a(0, 8), b(0, 8);
+    const bool loaded = a.loadNetwork("/nonexistent/model.hvmw", "");
+    std::vector<__half> obs(8 * HM_NB_INPUT_VALUES);
+    hm::BatchingEngine::HalfInferenceOutputs out;
+    const bool ran = a.runInferenceHalf(obs.data(), out, 0);
+    const bool synced_without_request = b.synchronizeInferenceHalf(out, 1);
+    std::printf("loaded %d ran %d synced %d slots %d large %d\n", loaded, ran, synced_without_request,
+                a.backend().slotsTotal(), a.backend().largeBatch());
+    return 0;
+}
+''')
+    out = tmp_path / "b"
+    cmd = ["g++", "-O1", "-std=c++17", "-I" + os.path.join(ROOT, "include"), str(src), "-L" + os.path.dirname(lib), "-lhm_engine",
+           "-Wl,-rpath," + os.path.dirname(lib), "-lpthread", "-o", str(out)]
+    if os.path.isdir("/usr/local/cuda/include"):
+        cmd.insert(4, "-I/usr/local/cuda/include")
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run(["timeout", "60", str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "loaded 0" in r.stdout and "synced 0" in r.stdout and "slots 128 large 512" in r.stdout
+    if not torch.cuda.is_available():
+        assert "ran 0" in r.stdout
