@@ -248,9 +248,7 @@ static int enqueue_positions_impl(hm_engine* h, const hm_packed_pos* pos, size_t
     std::memcpy(w->h_offsets, move_offsets, (2 * n_pos + 1) * 4);
     for (size_t i = 2 * n_pos + 1; i < 2 * B + 1; ++i) w->h_offsets[i] = static_cast<uint32_t>(n_moves);
     cudaStream_t s = w->stream;
-    bool ok = cuda_ok(cudaMemcpyAsync(w->d_pos, w->h_pos, B * sizeof(hm_packed_pos), cudaMemcpyHostToDevice, s), "H2D pos") &&
-              cuda_ok(cudaMemcpyAsync(w->d_offsets, w->h_offsets, (2 * B + 1) * 4, cudaMemcpyHostToDevice, s), "H2D offsets");
-    if (ok && n_moves) ok = cuda_ok(cudaMemcpyAsync(w->d_moves, w->h_moves, n_moves * 4, cudaMemcpyHostToDevice, s), "H2D moves");
+    bool ok = cuda_ok(cudaMemcpyAsync(w->d_in, w->h_in, w->in_fixed + n_moves * 4, cudaMemcpyHostToDevice, s), "H2D request");
     if (rp) {  // inputs of the root stages ride along with the request
         RootPolicyArgs a;
         a.temperature = rp->temperature;
@@ -283,9 +281,7 @@ static int enqueue_positions_impl(hm_engine* h, const hm_packed_pos* pos, size_t
     } else {
         ok = ok && cuda_ok(cudaGraphLaunch(w->graph_fused, s), "graph launch");
     }
-    if (ok && n_moves) ok = cuda_ok(cudaMemcpyAsync(w->h_priors, w->d_priors, n_moves * 4, cudaMemcpyDeviceToHost, s), "D2H priors");
-    ok = ok && cuda_ok(cudaMemcpyAsync(w->h_values, w->d_values, B * 4, cudaMemcpyDeviceToHost, s), "D2H values") &&
-         cuda_ok(cudaMemcpyAsync(w->h_raw5, w->d_raw5, B * 5 * 4, cudaMemcpyDeviceToHost, s), "D2H raw");
+    ok = ok && cuda_ok(cudaMemcpyAsync(w->h_out, w->d_out, w->out_fixed + n_moves * 4, cudaMemcpyDeviceToHost, s), "D2H results");
     if (!ok) return 0;
     w->pending = true;
     w->pending_kind = rp ? 3 : 2;

@@ -706,20 +706,38 @@ static bool setup_worker(Engine* e, Worker& w) {
     if (!cuda_ok(cudaStreamCreateWithFlags(&w.side_stream, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
     if (!cuda_ok(cudaEventCreateWithFlags(&w.ev_fork, cudaEventDisableTiming), "cudaEventCreate") ||
         !cuda_ok(cudaEventCreateWithFlags(&w.ev_join, cudaEventDisableTiming), "cudaEventCreate")) return false;
-    bool ok = dev_alloc(w, &w.d_pos, nb) && dev_alloc(w, &w.d_moves, w.move_cap) &&
-              dev_alloc(w, &w.d_offsets, 2 * nb + 1) && dev_alloc(w, &w.d_priors, w.move_cap) &&
-              dev_alloc(w, &w.d_values, nb) && dev_alloc(w, &w.d_planes, nb * HM_NB_INPUT_VALUES) &&
+    // The request inputs (records | offsets | moves) and the results (values | raw5 | priors) of the fused
+    // path each live in ONE device block mirrored by ONE pinned block: a request is one H2D and one D2H
+    // copy of (fixed part + 4 bytes per move) instead of three each.
+    auto up16 = [](size_t v) { return (v + 15) & ~static_cast<size_t>(15); };
+    w.in_fixed = up16(nb * sizeof(hm_packed_pos) + (2 * nb + 1) * 4);
+    w.out_fixed = up16(nb * 4 + nb * 5 * 4);
+    uint8_t *d_in = nullptr, *d_out = nullptr, *h_in = nullptr, *h_out = nullptr;
+    bool ok = dev_alloc(w, &d_in, w.in_fixed + w.move_cap * 4) && dev_alloc(w, &d_out, w.out_fixed + w.move_cap * 4) &&
+              host_alloc(w, &h_in, w.in_fixed + w.move_cap * 4) && host_alloc(w, &h_out, w.out_fixed + w.move_cap * 4);
+    if (!ok) return false;
+    w.d_in = d_in; w.d_out = d_out; w.h_in = h_in; w.h_out = h_out;
+    w.d_pos = reinterpret_cast<hm_packed_pos*>(d_in);
+    w.d_offsets = reinterpret_cast<uint32_t*>(d_in + nb * sizeof(hm_packed_pos));
+    w.d_moves = reinterpret_cast<uint32_t*>(d_in + w.in_fixed);
+    w.h_pos = reinterpret_cast<hm_packed_pos*>(h_in);
+    w.h_offsets = reinterpret_cast<uint32_t*>(h_in + nb * sizeof(hm_packed_pos));
+    w.h_moves = reinterpret_cast<uint32_t*>(h_in + w.in_fixed);
+    w.d_values = reinterpret_cast<float*>(d_out);
+    w.d_raw5 = reinterpret_cast<float*>(d_out + nb * 4);
+    w.d_priors = reinterpret_cast<float*>(d_out + w.out_fixed);
+    w.h_values = reinterpret_cast<float*>(h_out);
+    w.h_raw5 = reinterpret_cast<float*>(h_out + nb * 4);
+    w.h_priors = reinterpret_cast<float*>(h_out + w.out_fixed);
+    ok = dev_alloc(w, &w.d_planes, nb * HM_NB_INPUT_VALUES) &&
               dev_alloc(w, &w.d_trunk, nb * 384 * 64) && dev_alloc(w, &w.d_pol_shared, nb * 384 * 64) &&
               dev_alloc(w, &w.d_logits, nb * POLICY_CH * 64) && dev_alloc(w, &w.d_pi, nb * POLICY_CH * 64) &&
-              dev_alloc(w, &w.d_vfeat, nb * 16 * 64) && dev_alloc(w, &w.d_raw5, nb * 5) &&
+              dev_alloc(w, &w.d_vfeat, nb * 16 * 64) &&
               dev_alloc(w, &w.d_value_h, nb) && dev_alloc(w, &w.d_wdl_h, nb * 3) && dev_alloc(w, &w.d_ml_h, nb) &&
               dev_alloc(w, &w.d_captures, w.move_cap) && dev_alloc(w, &w.d_noise, w.move_cap) &&
               dev_alloc(w, &w.d_hash, nb) && dev_alloc(w, &w.d_uniforms, nb * 3) &&
               dev_alloc(w, &w.d_picks, nb * 2) && dev_alloc(w, &w.d_status, nb);
-    ok = ok && host_alloc(w, &w.h_pos, nb) && host_alloc(w, &w.h_moves, w.move_cap) &&
-         host_alloc(w, &w.h_offsets, 2 * nb + 1) && host_alloc(w, &w.h_priors, w.move_cap) &&
-         host_alloc(w, &w.h_values, nb) && host_alloc(w, &w.h_raw5, nb * 5) &&
-         host_alloc(w, &w.h_obs, nb * HM_NB_INPUT_VALUES) && host_alloc(w, &w.h_value, nb) &&
+    ok = ok && host_alloc(w, &w.h_obs, nb * HM_NB_INPUT_VALUES) && host_alloc(w, &w.h_value, nb) &&
          host_alloc(w, &w.h_wdl, nb * 3) && host_alloc(w, &w.h_ml, nb) &&
          host_alloc(w, &w.h_pi_a, nb * HM_NB_POLICY_VALUES) && host_alloc(w, &w.h_pi_b, nb * HM_NB_POLICY_VALUES) &&
          host_alloc(w, &w.h_captures, w.move_cap) && host_alloc(w, &w.h_hash, nb) &&

@@ -114,7 +114,10 @@ struct Worker {
     int pending_kind = 0;  // 1 = dense half request, 2 = packed positions request, 3 = positions + root stages
     size_t pending_npos = 0, pending_nmoves = 0;
 
-    // device arena
+    // device arena.  d_pos | d_offsets | d_moves are consecutive pieces of d_in, d_values | d_raw5 | d_priors
+    // of d_out (pinned mirrors h_in / h_out): one copy each way per fused request
+    uint8_t *d_in = nullptr, *d_out = nullptr, *h_in = nullptr, *h_out = nullptr;
+    size_t in_fixed = 0, out_fixed = 0;   // bytes before the per-move part of each block
     hm_packed_pos* d_pos = nullptr;
     uint32_t* d_moves = nullptr;
     uint32_t* d_offsets = nullptr;
