@@ -69,6 +69,7 @@ SYMBOLS = {
     "hm_policy_priors_half": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _vp]),
     "hm_policy_indices": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "hm_shape_values_half": (_i, [_vp, _vp, _vp, _vp, _sz, _vp]),
+    "hm_engine_bench_e2e": (_i, [_vp, _vp, _sz, _vp, _vp, _i, _i, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "hm_bench_planes": (_i, [_vp, _vp, _sz, _i, _i, C.POINTER(C.c_float)]),
     "hm_bench_priors": (_i, [_vp, _vp, _sz, _vp, _vp, _i, C.POINTER(C.c_float)]),
     "hm_engine_bench_resident": (_i, [_vp, _sz, _i, C.POINTER(C.c_float), C.POINTER(_i)]),

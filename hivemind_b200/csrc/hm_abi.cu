@@ -1,5 +1,6 @@
 // hm_abi.cu — the C ABI declared in include/hm_engine.h (drop-in boundary for the
 // reference's nn/ Engine, engine/src/nn/engine.h:43-132).  Never throws; returns 0/1.
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -601,6 +602,40 @@ int hm_bench_priors(hm_engine* h, const hm_packed_pos* pos, size_t n_pos, const 
         ok = cuda_ok(cudaMemcpyAsync(dl.p + p * row.size(), row.data(), row.size() * 4, cudaMemcpyHostToDevice, s), "H2D logits");
     if (!ok) return 0;
     return time_launches(s, iters, [&] { launch_policy_priors_packed(dl.p, dpos.p, static_cast<int>(n_pos), dm.p, doff.p, dp.p, s); }, ms_total) ? 1 : 0;
+    HM_CATCH(0)
+}
+
+int hm_engine_bench_e2e(hm_engine* h, const hm_packed_pos* pos, size_t n_pos, const uint32_t* moves,
+                        const uint32_t* move_offsets, int iters, int slots, double* ms_total, double* checksum) {
+    HM_TRY
+    if (!h || !pos || !move_offsets || iters <= 0) { set_error("bad argument"); return 0; }
+    slots = std::max(1, std::min<int>(slots, static_cast<int>(h->e.workers.size())));
+    const float* values = nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    int in_flight = 0, next_sync = 0;
+    for (int i = 0; i < iters; ++i) {
+        const int w = i % slots;
+        if (in_flight == slots) {
+            if (!hm_engine_sync_priors(h, next_sync, nullptr, &values, nullptr)) return 0;
+            next_sync = (next_sync + 1) % slots;
+            --in_flight;
+        }
+        if (!hm_engine_enqueue_positions(h, pos, n_pos, moves, move_offsets, w)) return 0;
+        ++in_flight;
+    }
+    while (in_flight > 0) {
+        if (!hm_engine_sync_priors(h, next_sync, nullptr, &values, nullptr)) return 0;
+        next_sync = (next_sync + 1) % slots;
+        --in_flight;
+    }
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    if (ms_total) *ms_total = ms;
+    if (checksum) {
+        double c = 0.0;
+        for (size_t i = 0; values && i < n_pos; ++i) c += values[i];
+        *checksum = c;
+    }
+    return 1;
     HM_CATCH(0)
 }
 

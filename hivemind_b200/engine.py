@@ -260,6 +260,18 @@ class Engine:
             raise RuntimeError(_lib.last_error())
         return ms.value, n.value
 
+    def benchE2E(self, pos, moves, offsets, iters: int, slots: int = 2):
+        """The enqueuePositions / synchronizePriors loop driven from C (as the reference's C++ caller would):
+        -> (wall ms for all iters incl. H2D/D2H, checksum of the last request's values)."""
+        pos = np.ascontiguousarray(pos)
+        moves = np.ascontiguousarray(moves, np.uint32)
+        offsets = np.ascontiguousarray(offsets, np.uint32)
+        ms, chk = C.c_double(), C.c_double()
+        if not self._L.hm_engine_bench_e2e(self._h, pos.ctypes.data, pos.shape[0], moves.ctypes.data, offsets.ctypes.data,
+                                           iters, slots, C.byref(ms), C.byref(chk)):
+            raise RuntimeError(_lib.last_error())
+        return ms.value, chk.value
+
     def benchPlanes(self, pos: np.ndarray, dtype: str = "f16", iters: int = 20) -> float:
         """Device-resident stand-alone plane encode of len(pos) positions -> ms per launch."""
         pos = np.ascontiguousarray(pos)

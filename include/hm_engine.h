@@ -255,6 +255,14 @@ int hm_bench_planes(hm_engine* e, const hm_packed_pos* pos, size_t n, int dtype,
 int hm_bench_priors(hm_engine* e, const hm_packed_pos* pos, size_t n_pos, const uint32_t* moves,
                     const uint32_t* move_offsets, int iters, float* ms_total);
 
+/* End-to-end loop as a C/C++ caller drives it: `iters` requests of hm_engine_enqueue_positions /
+ * hm_engine_sync_priors from the given HOST buffers, `slots` workers kept in flight round-robin
+ * (searchthread.cc:661-708 keeps one request per worker in flight).  Wall-clock milliseconds
+ * (std::chrono::steady_clock) from the first enqueue to the last sync, H2D and D2H included;
+ * *checksum = sum of the shaped values of the last request. */
+int hm_engine_bench_e2e(hm_engine* e, const hm_packed_pos* pos, size_t n_pos, const uint32_t* moves,
+                        const uint32_t* move_offsets, int iters, int slots, double* ms_total, double* checksum);
+
 /* Per-kernel timing of one pass with CUDA events between launches: fills up to `cap`
  * entries of (name, ms); returns the count in *n. */
 typedef struct hm_kernel_time {
