@@ -244,3 +244,72 @@ def test_crossboard_reference_shaped_half_path(cross_engine, oracle, gold_positi
     assert np.abs(out.policyA[:8].astype(np.float32) - f["pi_a_first8"]).max() <= 0.1
     assert np.abs(out.policyB[:8].astype(np.float32) - f["pi_b_first8"]).max() <= 0.1
     assert cross_engine._L.hm_engine_arch(cross_engine._h) == 1
+
+
+@pytest.mark.gpu
+def test_batching_engine_returns_the_direct_engine_outputs(tmp_path, blob):
+    """include/hm_batching_engine.hpp: 6 small-batch facades x 4 worker threads each, every (engine, worker) with its
+    own planes, coalesced into passes of one 512-row evaluator; each caller must get back, bit for bit, what a direct
+    batch-8 Engine returns for its 8 positions (and a second request on a busy worker is refused)."""
+    import os
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.join(root, "hivemind_b200")
+    src = tmp_path / "bt.cc"
+    src.write_text(r'''
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <thread>
+#include <vector>
+#include "hm_batching_engine.hpp"
+static void fill(std::vector<__half>& v, unsigned seed) {   // sparse 0/1 planes like real inputs
+    unsigned s = seed * 2654435761u + 12345u;
+    for (auto& x : v) { s = s * 1664525u + 1013904223u; x = __float2half(((s >> 24) & 7u) == 0u ? 1.0f : 0.0f); }
+}
+int main(int argc, char** argv) {
+    const int E = 6, W = 4, B = 8, ROUNDS = 5;
+    Engine direct(0, B, 1);
+    if (!direct.loadNetwork(argv[1])) return 2;
+    std::vector<std::unique_ptr<hm::BatchingEngine>> eng;
+    for (int e = 0; e < E; ++e) { eng.emplace_back(new hm::BatchingEngine(0, B)); if (!eng.back()->loadNetwork(argv[1])) return 3; }
+    std::atomic<int> bad{0};
+    std::vector<std::thread> th;
+    std::mutex dm;
+    for (int e = 0; e < E; ++e)
+        for (int w = 0; w < W; ++w)
+            th.emplace_back([&, e, w] {
+                std::vector<__half> obs(size_t(B) * HM_NB_INPUT_VALUES);
+                for (int r = 0; r < ROUNDS; ++r) {
+                    fill(obs, 1000u * e + 10u * w + r);
+                    hm::BatchingEngine::HalfInferenceOutputs o;
+                    if (!eng[e]->enqueueInferenceHalf(obs.data(), w)) { ++bad; return; }
+                    if (r == 0 && eng[e]->enqueueInferenceHalf(obs.data(), w)) ++bad;   // busy worker must refuse
+                    if (!eng[e]->synchronizeInferenceHalf(o, w)) { ++bad; return; }
+                    std::lock_guard<std::mutex> lock(dm);                               // the direct engine has one worker
+                    Engine::HalfInferenceOutputs d;
+                    if (!direct.runInferenceHalf(obs.data(), d, 0)) { ++bad; return; }
+                    if (std::memcmp(o.value, d.value, B * 2) || std::memcmp(o.policyA, d.policyA, size_t(B) * HM_NB_POLICY_VALUES * 2) ||
+                        std::memcmp(o.policyB, d.policyB, size_t(B) * HM_NB_POLICY_VALUES * 2) || std::memcmp(o.wdl, d.wdl, B * 6) ||
+                        std::memcmp(o.movesLeft, d.movesLeft, B * 2)) ++bad;
+                }
+            });
+    for (auto& t : th) t.join();
+    hm::BatchingBackend& be = eng[0]->backend();
+    std::printf("bad %d passes %ld rows %ld slots %d\n", bad.load(), be.passes(), be.rowsServed(), be.slotsTotal());
+    return bad.load() == 0 ? 0 : 1;
+}
+''')
+    exe = tmp_path / "bt"
+    cmd = ["g++", "-O1", "-std=c++17", "-I" + os.path.join(root, "include"), str(src), "-L" + lib_dir, "-lhm_engine",
+           "-Wl,-rpath," + lib_dir, "-lpthread", "-o", str(exe)]
+    if os.path.isdir("/usr/local/cuda/include"):
+        cmd.insert(4, "-I/usr/local/cuda/include")
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    w = tmp_path / "net.hvmw"
+    w.write_bytes(blob)
+    r = subprocess.run(["timeout", "300", str(exe), str(w)], capture_output=True, text=True, timeout=400)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "bad 0" in r.stdout and "rows 960" in r.stdout, r.stdout   # 6 engines x 4 workers x 5 rounds x 8 rows
