@@ -111,6 +111,39 @@ def test_short_and_ragged_batches(engine256, gold_positions, gold_forward):
     assert engine256.evaluatePositions(np.zeros(257, POS_DTYPE), np.zeros(0, np.uint32), np.zeros(515, np.uint32)) is None
 
 
+def test_maximum_move_lists_and_capacity(engine256, oracle, gold_positions):
+    """The arena holds 256 moves per board (2 x 256 x batch in all): a request that fills it exactly is evaluated
+    and agrees with the oracle softmax over the same logits; one move more is refused; offsets must not decrease."""
+    from hivemind_b200 import _lib
+
+    g = gold_positions
+    n, per = 256, 256
+    rng = np.random.default_rng(5)
+    pool = np.unique(g["all_moves"])
+    moves = rng.choice(pool, size=2 * n * per).astype(np.uint32)
+    moves[per - 1::per] = 0  # MOVE_NONE closes every list, as the reference builds them
+    offs = (np.arange(2 * n + 1) * per).astype(np.uint32)
+    res = engine256.evaluatePositions(g["packed"], moves, offs)
+    assert res is not None
+    priors = np.array(res[0], copy=True)
+    sums = priors.reshape(2 * n, per).sum(axis=1)
+    assert np.allclose(sums, 1.0, atol=1e-5) and np.all(priors >= 0)
+    logits = engine256.debugFetch("logits").reshape(n, 2, 4672)
+    for k in (0, 1, 255, 511):
+        p, b = k // 2, k % 2
+        stm = int(g["packed"][p]["board"][b]["flags"] & 1)
+        want = oracle.priors_f32(logits[p, b], moves[k * per:(k + 1) * per], stm)
+        assert np.allclose(priors[k * per:(k + 1) * per], want, rtol=0, atol=1e-6)
+    # one move over the arena capacity
+    over = np.concatenate([offs[:-1], [offs[-1] + 1]]).astype(np.uint32)
+    assert engine256.evaluatePositions(g["packed"], np.concatenate([moves, [0]]).astype(np.uint32), over) is None
+    assert "capacity" in _lib.last_error()
+    bad = offs.copy()
+    bad[3] = bad[2] - 1
+    assert engine256.evaluatePositions(g["packed"], moves, bad) is None
+    assert "non-decreasing" in _lib.last_error()
+
+
 def test_batch_invariance_and_determinism(engine256, gold_positions):
     g = gold_positions
     a = engine256.evaluatePositions(g["packed"], g["moves"], g["offsets"])
