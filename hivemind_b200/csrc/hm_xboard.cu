@@ -49,39 +49,47 @@ token_embed_kernel(const float* __restrict__ pre, const act_t* __restrict__ plan
     }
     const int sq = threadIdx.x & 63, grp = threadIdx.x >> 6;
     __syncthreads();
-    for (int pp = 0; pp < TE_POS; ++pp) {
-        const int pos = blockIdx.x * TE_POS + pp;
-        if (pos >= n) break;
-        float pl[40];
+    // two positions per step: one 16-byte weight broadcast feeds 8 FMAs instead of 4 (the loop was bound by the
+    // shared-memory weight reads, one LDS.128 per 4 FMAs)
+    for (int pp = 0; pp < TE_POS; pp += 2) {
+        const int pos0 = blockIdx.x * TE_POS + pp, pos1 = pos0 + 1;
+        if (pos0 >= n) break;
+        const bool has1 = pos1 < n;
+        float pl0[40], pl1[40];
 #pragma unroll
-        for (int c = 0; c < 37; ++c)
-            pl[c] = act_to_float(planes[(static_cast<size_t>(pos) * 74 + 37 * b + c) * 64 + sq]);
-        pl[37] = pl[38] = pl[39] = 0.0f;
-        const float* prow = pre + (static_cast<size_t>(pos) * 384 + b * XD) * 64 + sq;
-        act_t* trow = tok + (static_cast<size_t>(pos) * 384 + b * XD) * 64 + sq;
-        // 8 outputs per step: their `pre` / embedding loads are issued together, then the FMAs
+        for (int c = 0; c < 37; ++c) {
+            pl0[c] = act_to_float(planes[(static_cast<size_t>(pos0) * 74 + 37 * b + c) * 64 + sq]);
+            pl1[c] = has1 ? act_to_float(planes[(static_cast<size_t>(pos1) * 74 + 37 * b + c) * 64 + sq]) : 0.0f;
+        }
+        pl0[37] = pl0[38] = pl0[39] = pl1[37] = pl1[38] = pl1[39] = 0.0f;
+        const float* prow0 = pre + (static_cast<size_t>(pos0) * 384 + b * XD) * 64 + sq;
+        const float* prow1 = prow0 + (has1 ? 384 * 64 : 0);
+        act_t* trow0 = tok + (static_cast<size_t>(pos0) * 384 + b * XD) * 64 + sq;
+        act_t* trow1 = trow0 + 384 * 64;
 #pragma unroll 1
-        for (int o0 = grp * 48; o0 < grp * 48 + 48; o0 += 8) {
-            float v[8], e[8];
+        for (int o0 = grp * 48; o0 < grp * 48 + 48; o0 += 4) {
+            float v0[4], v1[4], e[4];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                v[j] = prow[(o0 + j) * 64];
+            for (int j = 0; j < 4; ++j) {
+                v0[j] = prow0[(o0 + j) * 64];
+                v1[j] = prow1[(o0 + j) * 64];
                 e[j] = pos_emb[(o0 + j) * 64 + sq];
             }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < 4; ++j) {
                 const int o = o0 + j;
-                float a = v[j] + s_add[o];
+                float a0 = v0[j] + s_add[o], a1 = v1[j] + s_add[o];
                 const float4* w = reinterpret_cast<const float4*>(s_wp + o * 40);
 #pragma unroll
                 for (int c4 = 0; c4 < 10; ++c4) {
                     const float4 ww = w[c4];
-                    a = fmaf(ww.x, pl[4 * c4], a);
-                    a = fmaf(ww.y, pl[4 * c4 + 1], a);
-                    a = fmaf(ww.z, pl[4 * c4 + 2], a);
-                    a = fmaf(ww.w, pl[4 * c4 + 3], a);
+                    a0 = fmaf(ww.x, pl0[4 * c4], a0);      a1 = fmaf(ww.x, pl1[4 * c4], a1);
+                    a0 = fmaf(ww.y, pl0[4 * c4 + 1], a0);  a1 = fmaf(ww.y, pl1[4 * c4 + 1], a1);
+                    a0 = fmaf(ww.z, pl0[4 * c4 + 2], a0);  a1 = fmaf(ww.z, pl1[4 * c4 + 2], a1);
+                    a0 = fmaf(ww.w, pl0[4 * c4 + 3], a0);  a1 = fmaf(ww.w, pl1[4 * c4 + 3], a1);
                 }
-                trow[o * 64] = float_to_act(fmaxf(a, 0.0f) + e[j] + s_emb[o]);
+                trow0[o * 64] = float_to_act(fmaxf(a0, 0.0f) + e[j] + s_emb[o]);
+                if (has1) trow1[o * 64] = float_to_act(fmaxf(a1, 0.0f) + e[j] + s_emb[o]);
             }
         }
     }
@@ -171,7 +179,7 @@ __global__ void __launch_bounds__(384)
 context_kv_kernel(const float* __restrict__ ctx, const float* __restrict__ g, const float* __restrict__ b,
                   const float* __restrict__ wkv_t, const float* __restrict__ bkv, float* __restrict__ ckv, int n) {
     constexpr int NT = CKV_POS * XCTX;   // 28 tokens
-    __shared__ float s_n[NT][XD];
+    __shared__ __align__(16) float s_n[NT][XD];
     __shared__ float s_stat[NT][2];
     const int pos0 = blockIdx.x * CKV_POS;
     const int n_tok = min(CKV_POS, n - pos0) * XCTX;
@@ -197,10 +205,19 @@ context_kv_kernel(const float* __restrict__ ctx, const float* __restrict__ g, co
     float acc[NT];
 #pragma unroll
     for (int t = 0; t < NT; ++t) acc[t] = bkv[o];
-    for (int i = 0; i < XD; ++i) {
-        const float w = wkv_t[i * 384 + o];
+    // four input channels per step: the normalised tokens come out of shared memory as one 16-byte
+    // broadcast per (token, step) instead of four 4-byte ones (the loop was LDS-bound: one LDS per FMA)
+    for (int i = 0; i < XD; i += 4) {
+        const float w0 = wkv_t[i * 384 + o], w1 = wkv_t[(i + 1) * 384 + o];
+        const float w2 = wkv_t[(i + 2) * 384 + o], w3 = wkv_t[(i + 3) * 384 + o];
 #pragma unroll
-        for (int t = 0; t < NT; ++t) acc[t] = fmaf(w, s_n[t][i], acc[t]);
+        for (int t = 0; t < NT; ++t) {
+            const float4 sv = *reinterpret_cast<const float4*>(&s_n[t][i]);
+            acc[t] = fmaf(w0, sv.x, acc[t]);   // same order of accumulation as the one-channel loop
+            acc[t] = fmaf(w1, sv.y, acc[t]);
+            acc[t] = fmaf(w2, sv.z, acc[t]);
+            acc[t] = fmaf(w3, sv.w, acc[t]);
+        }
     }
 #pragma unroll
     for (int t = 0; t < NT; ++t)
