@@ -10,6 +10,7 @@
 #include <mutex>
 
 #include "hm_cgemm.cuh"
+#include "hm_lgemm.cuh"
 #include "hm_pgemm.cuh"
 #include "hm_trunk.cuh"
 #include "hm_kernels.h"
@@ -428,7 +429,9 @@ static bool kernels_prepare() {
         ok = cuda_ok(cudaFuncSetAttribute(cgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CG_SMEM),
                      "cudaFuncSetAttribute(cgemm)") &&
              cuda_ok(cudaFuncSetAttribute(trunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM),
-                     "cudaFuncSetAttribute(trunk)");
+                     "cudaFuncSetAttribute(trunk)") &&
+             cuda_ok(cudaFuncSetAttribute(lgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          lg_smem_bytes(LG_MAX_KPAIRS)), "cudaFuncSetAttribute(lgemm)");
     });
     return ok;
 }
@@ -532,6 +535,20 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
     op.klass = "dense";
     op.flops = 2.0 * L.macs_per_pos() * io.in_n;
     op.bytes = 0;
+    // wide shallow-K 1x1 layers (the crossboard Linears / projections): persistent CTAs with resident weights
+    // and two TMEM accumulators (hm_lgemm.cuh) instead of one latency-bound CTA per tile; HM_NO_LGEMM=1 opts out
+    const int kpairs = p.kblocks / 2, n_tiles = io.in_n / 2;
+    if (L.ksize == 1 && L.cout >= 128 && kpairs <= LG_MAX_KPAIRS && n_tiles >= 148 && getenv("HM_NO_LGEMM") == nullptr) {
+        int n_sm = 148;
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
+        const dim3 lgrid(static_cast<unsigned>(std::max(1, std::min(n_tiles, n_sm / p.m_blocks))), static_cast<unsigned>(p.m_blocks));
+        const int lsmem = lg_smem_bytes(kpairs);
+        op.launch = [p, tm_w, tm_x, lgrid, lsmem, n_tiles](cudaStream_t s) {
+            lgemm_kernel<<<lgrid, LG_THREADS, lsmem, s>>>(p, n_tiles, tm_w, tm_x);
+        };
+        ops.push_back(std::move(op));
+        return true;
+    }
     op.launch = [p, tm_w, tm_x, grid, smem](cudaStream_t s) {
         cgemm_kernel<<<grid, CG_THREADS, smem, s>>>(p, tm_w, tm_x);
     };
