@@ -614,6 +614,11 @@ static void add_simple(std::vector<Op>& ops, const std::string& name, const char
 // context tokens, the attention blocks, value fusion; leaves the final tokens in *tok_out and
 // the fused value input in w.d_fuse.
 static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int B, act_t** tok_out) {
+    // The 7 context tokens and their K|V for every attention layer depend on the input planes only
+    // (rise_mobile_v3.py:353-369: the layers never update them), so they are issued FIRST in the op list and
+    // captured as a graph branch that runs beside the stem and the trunk (capture_graph, "ctx." ops).
+    std::vector<Op> ctx_ops;
+    if (net.xlayers.size() > 2) { set_error("more than 2 cross-board layers are not supported"); return false; }
     const size_t nb = static_cast<size_t>(B);
     bool ok = dev_alloc(w, &w.d_tokpre, nb * 384 * 64) && dev_alloc(w, &w.d_tok[0], nb * 384 * 64) &&
               dev_alloc(w, &w.d_tok[1], nb * 384 * 64) && dev_alloc(w, &w.d_nq, nb * 384 * 64) &&
@@ -621,7 +626,7 @@ static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int 
               dev_alloc(w, &w.d_kv, nb * 768 * 64) && dev_alloc(w, &w.d_att, nb * 384 * 64) &&
               dev_alloc(w, &w.d_x1, nb * 384 * 64) && dev_alloc(w, &w.d_h, nb * 768 * 64) &&
               dev_alloc(w, &w.d_fuse, nb * 384 * 64) && dev_alloc(w, &w.d_ctx, nb * 7 * 192) &&
-              dev_alloc(w, &w.d_ckv, nb * 7 * 384);
+              dev_alloc(w, &w.d_ckv, 2 * nb * 7 * 384);   // one K|V block per attention layer
     if (!ok || !xboard_prepare()) return false;
     // X1/X2: trunk part of both token projections on the tensor cores, the 37 board planes,
     // BN bias, ReLU and the embeddings in the follow-up kernel
@@ -636,7 +641,7 @@ static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int 
                    [=](cudaStream_t s) { launch_token_embed(pre, planes, wp, tb, pe, be, tok, B, s); });
         const float *pw = net.pocket_w, *pb = net.pocket_b, *sw = net.scalar_w, *sb = net.scalar_b, *role = net.ctx_role;
         float* ctx = w.d_ctx;
-        add_simple(ops, "tokens.context", "tokens", nb * 7 * 192 * 4.0,
+        add_simple(ctx_ops, "ctx.tokens", "tokens", nb * 7 * 192 * 4.0,
                    [=](cudaStream_t s) { launch_context_tokens(planes, pw, pb, sw, sb, role, ctx, B, s); });
     }
     w.debug_views["tokens0"] = {w.d_tok[0], {B, 384 * 64, 0}};
@@ -647,7 +652,7 @@ static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int 
         const std::string q = "xl" + std::to_string(l) + ".";
         act_t *tin = w.d_tok[cur], *tout = w.d_tok[cur ^ 1];
         act_t *nq = w.d_nq, *nm = w.d_nm, *att = w.d_att, *x1 = w.d_x1, *qb = w.d_q, *kv = w.d_kv;
-        float *ctx = w.d_ctx, *ckv = w.d_ckv;
+        float *ctx = w.d_ctx, *ckv = w.d_ckv + (l & 1) * nb * 7 * 384;
         const float *qg = L.qn_g, *qbb = L.qn_b, *mg = L.mn_g, *mb = L.mn_b, *lg = L.ln_g, *lb = L.ln_b;
         add_simple(ops, q + "norm_qm", "tokens", nb * 384 * 64 * 6.0,
                    [=](cudaStream_t s) { launch_token_layernorm(tin, qg, qbb, nq, mg, mb, nm, 2 * B, s); });
@@ -657,7 +662,7 @@ static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int 
         io.in = nm; io.out = kv;
         if (!add_dense_io(ops, L.wkv, io)) return false;
         const float *wkv_t = L.wkv_t, *bkv = L.bkv;
-        add_simple(ops, q + "context_kv", "tokens", nb * 7 * 384 * 4.0,
+        add_simple(ctx_ops, "ctx.kv" + std::to_string(l), "tokens", nb * 7 * 384 * 4.0,
                    [=](cudaStream_t s) { launch_context_kv(ctx, mg, mb, wkv_t, bkv, ckv, B, s); });
         add_simple(ops, q + "attention", "attention", nb * 2 * (192.0 + 384 + 192) * 64 * 2,
                    [=](cudaStream_t s) { launch_cross_attention(qb, kv, ckv, att, B, s); });
@@ -681,6 +686,7 @@ static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int 
     DenseIO io;
     io.in = *tok_out; io.in_n = B; io.in_C = 384; io.out = w.d_fuse; io.act = 1;
     if (!add_dense_io(ops, net.vfuse, io)) return false;
+    ops.insert(ops.begin(), std::make_move_iterator(ctx_ops.begin()), std::make_move_iterator(ctx_ops.end()));
     w.debug_views["value_fusion"] = {w.d_fuse, {B, 384 * 64, 0}};
     return true;
 }
@@ -693,17 +699,34 @@ static bool capture_graph(Worker& w, const std::vector<const std::vector<Op>*>& 
     cudaGraph_t graph = nullptr;
     const bool branch = getenv("HM_NO_GRAPH_BRANCH") == nullptr;
     if (!cuda_ok(cudaStreamBeginCapture(w.stream, cudaStreamCaptureModeThreadLocal), "BeginCapture")) return false;
-    bool forked = false;
+    bool forked = false, forked2 = false, joined2 = false;
+    auto join2 = [&] {
+        if (forked2 && !joined2) {
+            cudaEventRecord(w.ev_join2, w.ctx_stream);
+            cudaStreamWaitEvent(w.stream, w.ev_join2, 0);
+            joined2 = true;
+        }
+    };
     for (auto* l : lists)
         for (const Op& op : *l) {
             const bool side = branch && op.name.rfind("value.", 0) == 0;
+            // context-token branch: forked where the ctx.* ops stand (right after the planes are there),
+            // joined before the first attention core, its only consumer
+            const bool ctx = branch && op.name.rfind("ctx.", 0) == 0;
+            if (ctx && !forked2) {
+                cudaEventRecord(w.ev_fork2, w.stream);
+                cudaStreamWaitEvent(w.ctx_stream, w.ev_fork2, 0);
+                forked2 = true;
+            }
+            if (op.name.size() > 10 && op.name.compare(op.name.size() - 10, 10, ".attention") == 0) join2();
             if (side && !forked) {
                 cudaEventRecord(w.ev_fork, w.stream);
                 cudaStreamWaitEvent(w.side_stream, w.ev_fork, 0);
                 forked = true;
             }
-            op.launch(side ? w.side_stream : w.stream);
+            op.launch(ctx ? w.ctx_stream : side ? w.side_stream : w.stream);
         }
+    join2();
     if (forked) {
         cudaEventRecord(w.ev_join, w.side_stream);
         cudaStreamWaitEvent(w.stream, w.ev_join, 0);
@@ -723,6 +746,9 @@ static bool setup_worker(Engine* e, Worker& w) {
     if (!cuda_ok(cudaStreamCreateWithFlags(&w.side_stream, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
     if (!cuda_ok(cudaEventCreateWithFlags(&w.ev_fork, cudaEventDisableTiming), "cudaEventCreate") ||
         !cuda_ok(cudaEventCreateWithFlags(&w.ev_join, cudaEventDisableTiming), "cudaEventCreate")) return false;
+    if (!cuda_ok(cudaStreamCreateWithFlags(&w.ctx_stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
+        !cuda_ok(cudaEventCreateWithFlags(&w.ev_fork2, cudaEventDisableTiming), "cudaEventCreate") ||
+        !cuda_ok(cudaEventCreateWithFlags(&w.ev_join2, cudaEventDisableTiming), "cudaEventCreate")) return false;
     // The request inputs (records | offsets | moves) and the results (values | raw5 | priors) of the fused
     // path each live in ONE device block mirrored by ONE pinned block: a request is one H2D and one D2H
     // copy of (fixed part + 4 bytes per move) instead of three each.
@@ -897,6 +923,9 @@ void engine_free_workers(Engine* e) {
         if (w->side_stream) cudaStreamDestroy(w->side_stream);
         if (w->ev_fork) cudaEventDestroy(w->ev_fork);
         if (w->ev_join) cudaEventDestroy(w->ev_join);
+        if (w->ctx_stream) cudaStreamDestroy(w->ctx_stream);
+        if (w->ev_fork2) cudaEventDestroy(w->ev_fork2);
+        if (w->ev_join2) cudaEventDestroy(w->ev_join2);
     }
     e->workers.clear();
 }

@@ -110,6 +110,8 @@ struct Worker {
     cudaStream_t stream = nullptr;
     cudaStream_t side_stream = nullptr;   // captured only: the value-head branch of the graphs
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t ctx_stream = nullptr;    // captured only: the context-token branch (ctx.* ops) beside the trunk
+    cudaEvent_t ev_fork2 = nullptr, ev_join2 = nullptr;
     bool pending = false;
     int pending_kind = 0;  // 1 = dense half request, 2 = packed positions request, 3 = positions + root stages
     size_t pending_npos = 0, pending_nmoves = 0;
