@@ -133,40 +133,85 @@ context_tokens_kernel(const act_t* __restrict__ planes, const float* __restrict_
 // ---- LayerNorm over the 192 channels of each token ----------------------------------------
 // x: [n2][192][64] (n2 = positions x boards).  One statistic, up to two affine outputs
 // (query_norm and memory_norm read the same tokens, rise_mobile_v3.py:263-268).
-// grid n2, 256 threads = 4 channel groups x 64 squares; each thread holds 48 channels.
+// grid n2, 256 threads = 32 channel groups x 8 square groups: a thread holds 6 channels x 8 squares and moves
+// them as 16-byte pieces (a warp = 4 channel groups x 8 square groups reads/writes 4 whole 128-byte rows per
+// instruction); the per-square statistics are reduced over the 32 channel groups through shared memory.
 __global__ void __launch_bounds__(256)
 token_layernorm_kernel(const act_t* __restrict__ x, const float* __restrict__ g1,
                        const float* __restrict__ b1, act_t* __restrict__ y1,
                        const float* __restrict__ g2, const float* __restrict__ b2,
                        act_t* __restrict__ y2) {
-    __shared__ float s_sum[4][64], s_sq[4][64];
+    __shared__ float s_part[32][65];   // [channel group][square] partial sums (padded: conflict-free columns)
+    __shared__ float s_stat[2][64];    // mean, rstd per square
     const size_t base = static_cast<size_t>(blockIdx.x) * XD * 64;
-    const int sq = threadIdx.x & 63, grp = threadIdx.x >> 6;
-    float v[48];
-    float s = 0.0f;
+    const int sg = threadIdx.x & 7, cg = threadIdx.x >> 3;   // squares 8*sg .., channels 6*cg ..
+    float v[6][8];
 #pragma unroll
-    for (int i = 0; i < 48; ++i) {
-        v[i] = act_to_float(x[base + static_cast<size_t>(grp * 48 + i) * 64 + sq]);
-        s += v[i];
+    for (int i = 0; i < 6; ++i) {
+        const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + base + static_cast<size_t>(cg * 6 + i) * 64 + sg * 8));
+        const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), c = unpack_act2(u.z), d = unpack_act2(u.w);
+        v[i][0] = a.x; v[i][1] = a.y; v[i][2] = b.x; v[i][3] = b.y;
+        v[i][4] = c.x; v[i][5] = c.y; v[i][6] = d.x; v[i][7] = d.y;
     }
-    s_sum[grp][sq] = s;
-    __syncthreads();
-    const float mean = (s_sum[0][sq] + s_sum[1][sq] + s_sum[2][sq] + s_sum[3][sq]) * (1.0f / XD);
-    float q = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 48; ++i) {
-        v[i] -= mean;
-        q = fmaf(v[i], v[i], q);
+    for (int k = 0; k < 8; ++k) {
+        float s = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) s += v[i][k];
+        s_part[cg][sg * 8 + k] = s;
     }
-    s_sq[grp][sq] = q;
     __syncthreads();
-    const float rstd = rsqrtf((s_sq[0][sq] + s_sq[1][sq] + s_sq[2][sq] + s_sq[3][sq]) * (1.0f / XD) + LN_EPS);
+    if (threadIdx.x < 64) {
+        float s = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 48; ++i) {
-        const int c = grp * 48 + i;
-        const float n = v[i] * rstd;
-        y1[base + static_cast<size_t>(c) * 64 + sq] = float_to_act(fmaf(n, g1[c], b1[c]));
-        if (y2 != nullptr) y2[base + static_cast<size_t>(c) * 64 + sq] = float_to_act(fmaf(n, g2[c], b2[c]));
+        for (int r = 0; r < 32; ++r) s += s_part[r][threadIdx.x];
+        s_stat[0][threadIdx.x] = s * (1.0f / XD);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float mean = s_stat[0][sg * 8 + k];
+        float q = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            v[i][k] -= mean;
+            q = fmaf(v[i][k], v[i][k], q);
+        }
+        s_part[cg][sg * 8 + k] = q;
+    }
+    __syncthreads();
+    if (threadIdx.x < 64) {
+        float q = 0.0f;
+#pragma unroll
+        for (int r = 0; r < 32; ++r) q += s_part[r][threadIdx.x];
+        s_stat[1][threadIdx.x] = rsqrtf(q * (1.0f / XD) + LN_EPS);
+    }
+    __syncthreads();
+    float rstd[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) rstd[k] = s_stat[1][sg * 8 + k];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const int c = cg * 6 + i;
+        const size_t off = base + static_cast<size_t>(c) * 64 + sg * 8;
+        {
+            const float g = g1[c], b = b1[c];
+            uint4 o;
+            o.x = pack_act2(fmaf(v[i][0] * rstd[0], g, b), fmaf(v[i][1] * rstd[1], g, b));
+            o.y = pack_act2(fmaf(v[i][2] * rstd[2], g, b), fmaf(v[i][3] * rstd[3], g, b));
+            o.z = pack_act2(fmaf(v[i][4] * rstd[4], g, b), fmaf(v[i][5] * rstd[5], g, b));
+            o.w = pack_act2(fmaf(v[i][6] * rstd[6], g, b), fmaf(v[i][7] * rstd[7], g, b));
+            *reinterpret_cast<uint4*>(y1 + off) = o;
+        }
+        if (y2 != nullptr) {
+            const float g = g2[c], b = b2[c];
+            uint4 o;
+            o.x = pack_act2(fmaf(v[i][0] * rstd[0], g, b), fmaf(v[i][1] * rstd[1], g, b));
+            o.y = pack_act2(fmaf(v[i][2] * rstd[2], g, b), fmaf(v[i][3] * rstd[3], g, b));
+            o.z = pack_act2(fmaf(v[i][4] * rstd[4], g, b), fmaf(v[i][5] * rstd[5], g, b));
+            o.w = pack_act2(fmaf(v[i][6] * rstd[6], g, b), fmaf(v[i][7] * rstd[7], g, b));
+            *reinterpret_cast<uint4*>(y2 + off) = o;
+        }
     }
 }
 
