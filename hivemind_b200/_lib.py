@@ -64,7 +64,7 @@ SYMBOLS = {
     "hm_root_policy_apply": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, C.POINTER(RootPolicy), _vp, _vp, _vp]),
     "hm_engine_enqueue_positions_root": (_i, [_vp, _vp, _sz, _vp, _vp, C.POINTER(RootPolicy), _sz]),
     "hm_engine_sync_root": (_i, [_vp, _sz, _pp, _pp, _pp, _pp, _pp]),
-    "hm_engine_set_value_config": (None, [_vp, C.POINTER(ValueConfig)]),
+    "hm_engine_set_value_config": (C.c_int, [_vp, C.POINTER(ValueConfig)]),
     "hm_encode_planes": (_i, [_vp, _vp, _sz, _vp, _i]),
     "hm_policy_priors_half": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _vp]),
     "hm_policy_indices": (_i, [_vp, _vp, _vp, _sz, _vp]),

@@ -7,6 +7,8 @@
 #include <functional>
 #include <mutex>
 
+#include <sys/stat.h>
+
 #include "hm_kernels.h"
 #include "hm_net.h"
 
@@ -94,6 +96,11 @@ hm_engine* hm_engine_create(int device, int batch, int n_workers) {
     h->e.batch = batch;
     h->e.n_workers = n_workers;
     if (!cuda_ok(cudaStreamCreateWithFlags(&h->e.util_stream, cudaStreamNonBlocking), "cudaStreamCreate")) { delete h; return nullptr; }
+    if (!cuda_ok(cudaMalloc(reinterpret_cast<void**>(&h->e.d_vcfg), sizeof(hm_value_config)), "cudaMalloc(value config)") ||
+        !cuda_ok(cudaMemcpy(h->e.d_vcfg, &h->e.vcfg, sizeof(hm_value_config), cudaMemcpyHostToDevice), "upload value config")) {
+        hm_engine_destroy(h);
+        return nullptr;
+    }
     return h;
     HM_CATCH(nullptr)
 }
@@ -104,6 +111,7 @@ void hm_engine_destroy(hm_engine* h) {
     engine_free_workers(&h->e);
     h->e.net.reset();
     if (h->e.util_stream) cudaStreamDestroy(h->e.util_stream);
+    if (h->e.d_vcfg) cudaFree(h->e.d_vcfg);
     delete h;
 }
 
@@ -121,8 +129,20 @@ int hm_engine_load(hm_engine* h, const char* path) {
     if (!h || !path) { set_error("null argument"); return 0; }
     std::string p(path);
     const std::string onnx = ".onnx";
-    if (p.size() > onnx.size() && p.compare(p.size() - onnx.size(), onnx.size(), onnx) == 0)
-        p = p.substr(0, p.size() - onnx.size()) + ".hvmw";  // loadNetwork(onnxFile, ...) call sites
+    if (p.size() > onnx.size() && p.compare(p.size() - onnx.size(), onnx.size(), onnx) == 0) {
+        // loadNetwork(onnxFile, ...) call sites: the converted weights sit beside the export as <name>.hvmw.  A
+        // re-exported .onnx NEWER than its .hvmw means the conversion was not re-run: refuse rather than silently
+        // keep playing the old network (python -m hivemind_b200.weights <checkpoint> <name>.hvmw refreshes it).
+        const std::string hv = p.substr(0, p.size() - onnx.size()) + ".hvmw";
+        struct stat so, sh;
+        if (stat(p.c_str(), &so) == 0 && stat(hv.c_str(), &sh) == 0 &&
+            (so.st_mtim.tv_sec > sh.st_mtim.tv_sec ||
+             (so.st_mtim.tv_sec == sh.st_mtim.tv_sec && so.st_mtim.tv_nsec > sh.st_mtim.tv_nsec))) {
+            set_error(hv + " is older than " + p + ": re-run the weight conversion");
+            return 0;
+        }
+        p = hv;
+    }
     std::ifstream f(p, std::ios::binary | std::ios::ate);
     if (!f) { set_error("cannot open " + p); return 0; }
     HvmwBlob b;
@@ -383,15 +403,19 @@ int hm_engine_sync_priors(hm_engine* h, size_t worker, const float** priors, con
     HM_CATCH(0)
 }
 
-void hm_engine_set_value_config(hm_engine* h, const hm_value_config* cfg) {
-    if (!h || !cfg) return;
+int hm_engine_set_value_config(hm_engine* h, const hm_value_config* cfg) {
+    HM_TRY
+    if (!h || !cfg) { set_error("null argument"); return 0; }
+    // The configuration is a device-side struct the value.shape launch of every graph reads: changing it is one
+    // copy — no worker is rebuilt, no pinned output pointer handed out earlier is invalidated.  Refused while a
+    // request is in flight (its shaped values would be computed under an undefined mix of old and new settings).
+    for (auto& w : h->e.workers)
+        if (w && w->pending) { set_error("cannot change the value configuration with requests in flight"); return 0; }
+    if (!use_device(h)) return 0;
+    if (!cuda_ok(cudaMemcpy(h->e.d_vcfg, cfg, sizeof(hm_value_config), cudaMemcpyHostToDevice), "upload value config")) return 0;
     h->e.vcfg = *cfg;
-    if (h->e.net) {  // kernel arguments are baked into the graphs: rebuild them
-        for (auto& w : h->e.workers)
-            if (w && w->pending) cudaStreamSynchronize(w->stream);
-        cudaSetDevice(h->e.device);
-        engine_setup_workers(&h->e);
-    }
+    return 1;
+    HM_CATCH(0)
 }
 
 // ---- stand-alone stages -------------------------------------------------------------------

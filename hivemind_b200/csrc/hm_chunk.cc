@@ -177,6 +177,12 @@ size_t hm_sparse_policy_from_visits(const int32_t* policy_index, const int64_t* 
         uint64_t total = 0;
         for (size_t i = 0; i < n_edges; ++i) {
             if (visits[i] <= 0) continue;
+            // the reference throws for a visited edge without a policy label (selfplay.cc:392-398); -1 (not
+            // representable) or an index beyond the 4672 labels must never reach the chunk as a sparse target
+            if (policy_index[i] < 0 || policy_index[i] >= HM_NB_POLICY_VALUES) {
+                set_error("Move is absent from policy map");
+                return 0;
+            }
             by_index[static_cast<uint16_t>(policy_index[i])] += static_cast<uint64_t>(visits[i]);
             total += static_cast<uint64_t>(visits[i]);
         }

@@ -21,9 +21,14 @@ void launch_planes_nchw(const hm_packed_pos* pos, int n, void* out, int dtype, c
 // w4: [1024][4] fp32 (3 wdl rows + plys row of the Linear weights, feature index c*64+sq),
 // b4: [4].  raw5: [n,5] fp32 {value, wdl_loss, wdl_draw, wdl_win, moves_left};
 // half outputs may be null.
-void launch_value_tail(const act_t* feat, const float* w4, const float* b4, int n,
+// mlp: null, or the 49 floats of the use_mlp_wdl_ply value MLP (builder_util.py:292-296): [8][4] | [8] | [8] | [1].
+void launch_value_tail(const act_t* feat, const float* w4, const float* b4, const float* mlp, int n,
                        float* raw5, __half* value_h, __half* wdl_h, __half* ml_h,
                        cudaStream_t s);
+// tanh value head (builder_util.py:297-301, :326): w1t fp32 [1024 features][512 hidden], b1 [512], w2 [512], b2 [1];
+// raw5 = {value, NaN, NaN, NaN, 0}
+void launch_value_tanh(const act_t* feat, const float* w1t, const float* b1, const float* w2, const float* b2, int n,
+                       float* raw5, __half* value_h, __half* wdl_h, __half* ml_h, cudaStream_t s);
 
 // ---- stage X (crossboard-risev33, rise_mobile_v3.py:242-412), hm_xboard.cu ------------------------
 // tokens: fp16 [n][2 boards][192][64] channel-major; see the kernels for the formulas
@@ -52,7 +57,8 @@ void launch_policy_priors_dense(const __half* pi_a, const __half* pi_b, const hm
                                 float* priors, cudaStream_t s);
 void launch_policy_indices(const uint32_t* moves, const uint8_t* stm_black, int n, int32_t* out,
                            cudaStream_t s);
-void launch_shape_values_raw5(const float* raw5, int n, hm_value_config cfg, float* out,
+// cfg: DEVICE pointer (the engine's value configuration, updated in place by hm_engine_set_value_config)
+void launch_shape_values_raw5(const float* raw5, int n, const hm_value_config* cfg, float* out,
                               cudaStream_t s);
 void launch_shape_values_half(const __half* value, const __half* wdl, const __half* ml, int n,
                               hm_value_config cfg, float* out, cudaStream_t s);

@@ -56,7 +56,9 @@ bool HvmwBlob::parse() {
         std::memcpy(dims, e + 72, 16);
         std::memcpy(&off, e + 88, 8);
         std::memcpy(&nbytes, e + 96, 8);
-        if (dtype != 0 || ndim > 4 || off + nbytes > bytes.size() || (off & 3)) {
+        // overflow-safe bounds (off + nbytes may wrap for a crafted entry) and data must follow the table
+        const uint64_t size = bytes.size(), table_end = 64 + static_cast<uint64_t>(n) * 104;
+        if (dtype != 0 || ndim > 4 || off > size || nbytes > size - off || off < table_end || (off & 3)) {
             set_error(std::string("hvmw: bad entry ") + name);
             return false;
         }
@@ -354,11 +356,12 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
 
     // value head
     if (!make_dense(*net, net->value_conv, "value.conv", T("value.conv.w"), T("value.conv.b"))) return nullptr;
-    {
+    if (net->value_conv.cout != 16) { set_error("value head must have 16 channels"); return nullptr; }
+    if (T("value.wdl.w")) {
         const HvmwTensor *ww = T("value.wdl.w"), *wb = T("value.wdl.b"), *pw = T("value.plys.w"),
                          *pb = T("value.plys.b");
-        if (!ww || !wb || !pw || !pb || net->value_conv.cout != 16 || ww->numel() != 3 * 1024 || pw->numel() != 1024) {
-            set_error("value head tensors missing (WDL + plys configuration required)");
+        if (!ww || !wb || !pw || !pb || ww->numel() != 3 * 1024 || wb->numel() != 3 || pw->numel() != 1024 || pb->numel() != 1) {
+            set_error("malformed WDL / plys value head tensors");
             return nullptr;
         }
         std::vector<float> w4(1024 * 4), b4(4);
@@ -372,9 +375,59 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
         net->value_b4 = upload(*net, b4);
         if (!net->value_w4 || !net->value_b4) return nullptr;
         net->param_count += ww->numel() + wb->numel() + pw->numel() + pb->numel();
+        if (const HvmwTensor* m0 = T("value.mlp0.w")) {   // use_mlp_wdl_ply (builder_util.py:292-296)
+            const HvmwTensor *m0b = T("value.mlp0.b"), *m2 = T("value.mlp2.w"), *m2b = T("value.mlp2.b");
+            if (!m0b || !m2 || !m2b || m0->numel() != 32 || m0b->numel() != 8 || m2->numel() != 8 || m2b->numel() != 1) {
+                set_error("malformed value MLP tensors");
+                return nullptr;
+            }
+            std::vector<float> mlp(49);
+            std::copy(m0->data, m0->data + 32, mlp.begin());
+            std::copy(m0b->data, m0b->data + 8, mlp.begin() + 32);
+            std::copy(m2->data, m2->data + 8, mlp.begin() + 40);
+            mlp[48] = m2b->data[0];
+            if (!(net->value_mlp = upload(*net, mlp))) return nullptr;
+            net->param_count += 49;
+        }
+    } else {   // tanh value head (builder_util.py:297-301, :326)
+        const HvmwTensor *f0 = T("value.final0.w"), *f0b = T("value.final0.b"), *f2 = T("value.final2.w"), *f2b = T("value.final2.b");
+        if (!f0 || !f0b || !f2 || !f2b || f0->numel() != 512 * 1024 || f0b->numel() != 512 || f2->numel() != 512 || f2b->numel() != 1) {
+            set_error("value head tensors missing (WDL + plys heads or the 1024-512-1 tanh head)");
+            return nullptr;
+        }
+        std::vector<float> w1t(static_cast<size_t>(1024) * 512);
+        for (int j = 0; j < 512; ++j)
+            for (int i = 0; i < 1024; ++i) w1t[static_cast<size_t>(i) * 512 + j] = f0->data[static_cast<size_t>(j) * 1024 + i];
+        net->value_f0t = upload(*net, w1t);
+        if (!net->value_f0t || !(net->value_f0b = upload_tensor(*net, f0b, 512, "value.final0.b")) ||
+            !(net->value_f2w = upload_tensor(*net, f2, 512, "value.final2.w")) ||
+            !(net->value_f2b = upload_tensor(*net, f2b, 1, "value.final2.b"))) return nullptr;
+        net->param_count += f0->numel();
     }
     if (net->arch == HM_ARCH_CROSSBOARD_RISEV33) {
         if (!build_crossboard(*net, blob)) return nullptr;
+        return net;
+    }
+    if (T("pol0.c1.w")) {
+        // two independent _PolicyHead(384) (shared_policy_trunk=False, rise_mobile_v3.py:198-204, builder_util.py:206-243)
+        net->policy_per_board = true;
+        const HvmwTensor *a = T("pol0.c1.w"), *b = T("pol1.c1.w"), *ab = T("pol0.c1.b"), *bb = T("pol1.c1.b");
+        if (!a || !b || !ab || !bb || a->dims.size() != 4 || a->dims[0] != 384 || a->dims[1] != 384 || a->dims[2] != 3 ||
+            b->numel() != a->numel() || ab->numel() != 384 || bb->numel() != 384) {
+            set_error("per-board policy head tensors missing / malformed");
+            return nullptr;
+        }
+        std::vector<float> w(2 * a->numel()), bias(768);
+        std::copy(a->data, a->data + a->numel(), w.begin());
+        std::copy(b->data, b->data + b->numel(), w.begin() + a->numel());
+        std::copy(ab->data, ab->data + 384, bias.begin());
+        std::copy(bb->data, bb->data + 384, bias.begin() + 384);
+        if (!make_dense_raw(*net, net->pol_c1x, "policy.conv1", w.data(), 768, 384, 3, bias.data())) return nullptr;
+        for (int h = 0; h < 2; ++h) {
+            const std::string q = "pol" + std::to_string(h) + ".";
+            if (!make_dense(*net, net->pol_c2[h], "policy" + std::to_string(h) + ".conv2", T(q + "c2.w"), nullptr)) return nullptr;
+            if (net->pol_c2[h].cin != 384 || net->pol_c2[h].cout != 73 || net->pol_c2[h].ksize != 3) { set_error("unexpected policy head shape"); return nullptr; }
+        }
         return net;
     }
     // policy heads (shared trunk, two 73-channel projections stacked)
@@ -773,7 +826,7 @@ static bool setup_worker(Engine* e, Worker& w) {
     w.h_raw5 = reinterpret_cast<float*>(h_out + nb * 4);
     w.h_priors = reinterpret_cast<float*>(h_out + w.out_fixed);
     ok = dev_alloc(w, &w.d_planes, nb * HM_NB_INPUT_VALUES) &&
-              dev_alloc(w, &w.d_trunk, nb * 384 * 64) && dev_alloc(w, &w.d_pol_shared, nb * 384 * 64) &&
+              dev_alloc(w, &w.d_trunk, nb * 384 * 64) && dev_alloc(w, &w.d_pol_shared, nb * (net.policy_per_board ? 768 : 384) * 64) &&
               dev_alloc(w, &w.d_logits, nb * POLICY_CH * 64) && dev_alloc(w, &w.d_pi, nb * POLICY_CH * 64) &&
               dev_alloc(w, &w.d_vfeat, nb * 16 * 64) &&
               dev_alloc(w, &w.d_value_h, nb) && dev_alloc(w, &w.d_wdl_h, nb * 3) && dev_alloc(w, &w.d_ml_h, nb) &&
@@ -816,13 +869,17 @@ static bool setup_worker(Engine* e, Worker& w) {
         op.klass = "head";
         op.bytes = static_cast<double>(B) * 1024 * 2;
         const act_t* f = w.d_vfeat;
-        const float *w4 = net.value_w4, *b4 = net.value_b4;
+        const float *w4 = net.value_w4, *b4 = net.value_b4, *mlp = net.value_mlp;
+        const float *f0t = net.value_f0t, *f0b = net.value_f0b, *f2w = net.value_f2w, *f2b = net.value_f2b;
         float* raw5 = w.d_raw5;
         __half *vh = w.d_value_h, *wh = w.d_wdl_h, *mh = w.d_ml_h;
-        op.launch = [f, w4, b4, B, raw5, vh, wh, mh](cudaStream_t s) { launch_value_tail(f, w4, b4, B, raw5, vh, wh, mh, s); };
+        if (w4 != nullptr)
+            op.launch = [f, w4, b4, mlp, B, raw5, vh, wh, mh](cudaStream_t s) { launch_value_tail(f, w4, b4, mlp, B, raw5, vh, wh, mh, s); };
+        else   // tanh value head: 1024 -> 512 -> 1
+            op.launch = [f, f0t, f0b, f2w, f2b, B, raw5, vh, wh, mh](cudaStream_t s) { launch_value_tanh(f, f0t, f0b, f2w, f2b, B, raw5, vh, wh, mh, s); };
         ops.push_back(std::move(op));
     }
-    w.debug_views["policy_shared"] = {w.d_pol_shared, {B, 384 * 64, 0}};
+    w.debug_views["policy_shared"] = {w.d_pol_shared, {B, (net.policy_per_board ? 768 : 384) * 64, 0}};
     w.debug_views["logits"] = {w.d_logits, {B, POLICY_CH * 64, 1}};
     if (cross) {
         // per-board _PolicyHead(192) on that board's token map (rise_mobile_v3.py:336-347): board b's
@@ -837,6 +894,21 @@ static bool setup_worker(Engine* e, Worker& w) {
         for (int b = 0; b < 2; ++b) {
             DenseIO io;
             io.in = w.d_pol_shared + static_cast<size_t>(b) * 192 * 64; io.in_n = B; io.in_C = 192; io.in_stride_ch = 384;
+            io.out_channels = POLICY_CH;
+            io.out = w.d_pi + static_cast<size_t>(b) * 73 * 64; io.suffix = ".f16";
+            if (!add_narrow_io(w.ops_dense_out, net.pol_c2[b], io)) return false;
+            io.out = w.d_logits + static_cast<size_t>(b) * 73 * 64; io.out_f32 = true; io.suffix = "";
+            if (!add_narrow_io(w.ops_fused_out, net.pol_c2[b], io)) return false;
+        }
+    } else if (net.policy_per_board) {
+        // risev33 with two independent _PolicyHead(384): one stacked 384 -> 768 first conv over the trunk (board b's
+        // map = channels [384b, 384b+384) of d_pol_shared), then each board's 384 -> 73 conv into rows [73b, 73b+73)
+        DenseIO io;
+        io.in = w.d_trunk; io.in_n = B; io.in_C = 384; io.out = w.d_pol_shared; io.act = 1;
+        if (!add_dense_io(ops, net.pol_c1x, io)) return false;
+        for (int b = 0; b < 2; ++b) {
+            io = DenseIO();
+            io.in = w.d_pol_shared + static_cast<size_t>(b) * 384 * 64; io.in_n = B; io.in_C = 384; io.in_stride_ch = 768;
             io.out_channels = POLICY_CH;
             io.out = w.d_pi + static_cast<size_t>(b) * 73 * 64; io.suffix = ".f16";
             if (!add_narrow_io(w.ops_dense_out, net.pol_c2[b], io)) return false;
@@ -886,8 +958,8 @@ static bool setup_worker(Engine* e, Worker& w) {
         ov.bytes = static_cast<double>(B) * 24;
         const float* raw5 = w.d_raw5;
         float* vals = w.d_values;
-        const hm_value_config* cfg = &e->vcfg;  // read at launch time: graphs are re-captured on change
-        ov.launch = [raw5, B, cfg, vals](cudaStream_t s) { launch_shape_values_raw5(raw5, B, *cfg, vals, s); };
+        const hm_value_config* cfg = e->d_vcfg;  // device struct: a configuration change is a copy, not a re-capture
+        ov.launch = [raw5, B, cfg, vals](cudaStream_t s) { launch_shape_values_raw5(raw5, B, cfg, vals, s); };
         w.ops_fused_out.push_back(std::move(ov));
     }
     if (!capture_graph(w, {&w.ops_dense_in, &w.ops_trunk, &w.ops_dense_out}, &w.graph_dense)) return false;

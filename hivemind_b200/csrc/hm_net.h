@@ -78,8 +78,15 @@ struct Net {
     DenseLayer value_conv;       // 384 -> 16
     float* value_w4 = nullptr;   // [1024][4]
     float* value_b4 = nullptr;   // [4]
+    float* value_mlp = nullptr;  // use_mlp_wdl_ply value MLP (49 floats, hm_kernels.h) or null
+    // tanh value head (nets built without the WDL / plys heads, builder_util.py:297-301): present iff value_w4 is null
+    float *value_f0t = nullptr, *value_f0b = nullptr, *value_f2w = nullptr, *value_f2b = nullptr;
     DenseLayer policy_shared;    // 3x3 384 -> 384
     DenseLayer policy_proj;      // 3x3 384 -> 146 (A: 0..72, B: 73..145)
+    // risev33 with shared_policy_trunk=False (rise_mobile_v3.py:198-204): two _PolicyHead(384); the two 3x3
+    // 384->384 first convs are ONE stacked 384->768 layer over the trunk, the 384->73 second convs are pol_c2[]
+    bool policy_per_board = false;
+    DenseLayer pol_c1x;
     // crossboard-risev33 only (arch 1)
     DenseLayer tok_proj;          // 1x1 384 -> 384: trunk part of both board token projections stacked
     float *tok_wp = nullptr, *tok_bias = nullptr;      // [2][192][37], [2][192]
@@ -179,6 +186,7 @@ struct Engine {
     std::unique_ptr<Net> net;
     std::vector<std::unique_ptr<Worker>> workers;
     hm_value_config vcfg{1, 0.25f, 0.005f, 0.0f};  // search_params.h:122-128,148
+    hm_value_config* d_vcfg = nullptr;             // device copy read by the value.shape launch of every graph
     // scratch for the stand-alone stage entry points (guarded by a mutex)
     cudaStream_t util_stream = nullptr;
     void* util_mutex = nullptr;

@@ -223,10 +223,13 @@ __device__ __forceinline__ float shape_value(float value, float l, float d, floa
     return clampf(neural, -1.0f, 1.0f);
 }
 
-__global__ void shape_values_raw5_kernel(const float* __restrict__ raw5, int n, hm_value_config cfg,
+// cfg lives in device memory (one struct per engine): hm_engine_set_value_config updates it with a copy,
+// the captured graphs never have to be rebuilt
+__global__ void shape_values_raw5_kernel(const float* __restrict__ raw5, int n, const hm_value_config* __restrict__ cfgp,
                                          float* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const hm_value_config cfg = *cfgp;
     const float* r = raw5 + static_cast<size_t>(i) * 5;
     out[i] = shape_value(r[0], r[1], r[2], r[3], r[4], cfg);
 }
@@ -239,7 +242,7 @@ __global__ void shape_values_half_kernel(const __half* __restrict__ value,
     out[i] = shape_value(__half2float(value[i]), __half2float(wdl[3 * i]), __half2float(wdl[3 * i + 1]),
                          __half2float(wdl[3 * i + 2]), __half2float(ml[i]), cfg);
 }
-void launch_shape_values_raw5(const float* raw5, int n, hm_value_config cfg, float* out,
+void launch_shape_values_raw5(const float* raw5, int n, const hm_value_config* cfg, float* out,
                               cudaStream_t s) {
     if (n <= 0) return;
     shape_values_raw5_kernel<<<(n + 127) / 128, 128, 0, s>>>(raw5, n, cfg, out);

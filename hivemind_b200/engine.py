@@ -211,7 +211,7 @@ class Engine:
 
     def setValueConfig(self, enable_wdl_eval=True, wdl_value_weight=0.25, moves_left_discount=0.005, draw_contempt=0.0):
         cfg = ValueConfig(int(enable_wdl_eval), wdl_value_weight, moves_left_discount, draw_contempt)
-        self._L.hm_engine_set_value_config(self._h, C.byref(cfg))
+        return bool(self._L.hm_engine_set_value_config(self._h, C.byref(cfg)))
 
     # ---- stand-alone stages -------------------------------------------------------------
     def encodePlanes(self, pos: np.ndarray, dtype: str = "f32") -> np.ndarray:

@@ -25,7 +25,15 @@ ARCH_CROSSBOARD_RISEV33 = 1
 BN_EPS = 1e-5
 
 
-def risev33_spec() -> dict:
+def risev33_spec(shared_policy_trunk: bool = True, value_head: str = "wdl") -> dict:
+    """``shared_policy_trunk``: one 3x3 384->384 policy trunk + two 73-channel projections
+    (rise_mobile_v3.py:38-57, what train_loop.py:115 deploys) or, when False, two independent
+    ``_PolicyHead``s (builder_util.py:206-243, rise_mobile_v3.py:198-204).  ``value_head``:
+    "wdl" = WDL + plys heads, value = p_win - p_loss (builder_util.py:311-324, deployed);
+    "mlp" = the same heads plus the small value MLP on cat(wdl, plys) (``use_mlp_wdl_ply``, :292-296, :317-319);
+    "tanh" = no auxiliary heads, value = tanh(Linear(512,1)(relu(Linear(1024,512)))) (:297-301, :326)."""
+    if value_head not in ("wdl", "mlp", "tanh"):
+        raise ValueError(f"unknown value head {value_head!r}")
     kernels = [3] * 15
     for i in (7, 11, 12, 13):
         kernels[i] = 5
@@ -48,6 +56,8 @@ def risev33_spec() -> dict:
         "value_channels": 16,
         "value_fc": 512,
         "policy_channels": 73,
+        "shared_policy_trunk": bool(shared_policy_trunk),
+        "value_head": value_head,
     }
 
 
@@ -55,7 +65,7 @@ def crossboard_spec() -> dict:
     """``crossboard-risev33`` (rise_mobile_v3.py:852-888, class CrossBoardRiseV3 :281-412): the
     same stem + 15 blocks, then board tokens, 2 cross-board attention layers, value fusion and
     per-board 192-channel policy heads."""
-    spec = risev33_spec()
+    spec = risev33_spec(shared_policy_trunk=False)   # forced by the class itself, rise_mobile_v3.py:286-290
     spec.update({"arch": ARCH_CROSSBOARD_RISEV33, "attention_dim": 192, "attention_heads": 6,
                  "attention_layers": 2, "board_channels": 37, "mlp_ratio": 2})
     return spec
@@ -63,6 +73,20 @@ def crossboard_spec() -> dict:
 
 def spec_for_arch(arch: int) -> dict:
     return crossboard_spec() if arch == ARCH_CROSSBOARD_RISEV33 else risev33_spec()
+
+
+def spec_from_state_dict(sd) -> dict:
+    """The layer list a reference ``state_dict`` was built with, from its key names and shapes."""
+    if "value_head.body_wdl.0.weight" in sd:
+        value_head = "mlp" if tuple(np.shape(sd["value_head.body_final.0.weight"])) == (8, 4) else "wdl"
+    else:
+        value_head = "tanh"
+    if any(k.startswith("cross_board_blocks.0.") for k in sd):
+        spec = crossboard_spec()
+    else:
+        spec = risev33_spec(shared_policy_trunk="policy_heads.shared_body.0.weight" in sd)
+    spec["value_head"] = value_head
+    return spec
 
 
 def _bn(rng, c, prefix, sd, gamma_lo=0.5, gamma_hi=1.5):
@@ -102,23 +126,40 @@ def random_state_dict(spec: dict | None = None, seed: int = 0) -> Dict[str, np.n
     sd["value_head.body.0.weight"] = _conv(rng, (vc, C, 1, 1))
     _bn(rng, vc, "value_head.body.1", sd)
     nf = vc * 64
-    sd["value_head.body_wdl.0.weight"] = (rng.standard_normal((3, nf)) * (1.0 / np.sqrt(nf))).astype(np.float32)
-    sd["value_head.body_wdl.0.bias"] = (0.1 * rng.standard_normal(3)).astype(np.float32)
-    sd["value_head.body_plys.0.weight"] = (rng.standard_normal((1, nf)) * (1.5 / np.sqrt(nf))).astype(np.float32)
-    sd["value_head.body_plys.0.bias"] = (0.1 * rng.standard_normal(1)).astype(np.float32)
+    vh = spec.get("value_head", "wdl")
+    if vh != "tanh":
+        sd["value_head.body_wdl.0.weight"] = (rng.standard_normal((3, nf)) * (1.0 / np.sqrt(nf))).astype(np.float32)
+        sd["value_head.body_wdl.0.bias"] = (0.1 * rng.standard_normal(3)).astype(np.float32)
+        sd["value_head.body_plys.0.weight"] = (rng.standard_normal((1, nf)) * (1.5 / np.sqrt(nf))).astype(np.float32)
+        sd["value_head.body_plys.0.bias"] = (0.1 * rng.standard_normal(1)).astype(np.float32)
     fc = spec["value_fc"]
-    sd["value_head.body_final.0.weight"] = (rng.standard_normal((fc, nf)) / np.sqrt(nf)).astype(np.float32)
-    sd["value_head.body_final.0.bias"] = (0.1 * rng.standard_normal(fc)).astype(np.float32)
-    sd["value_head.body_final.2.weight"] = (rng.standard_normal((1, fc)) / np.sqrt(fc)).astype(np.float32)
-    sd["value_head.body_final.2.bias"] = (0.1 * rng.standard_normal(1)).astype(np.float32)
+    if vh == "mlp":   # builder_util.py:292-296: Linear(4,8) -> act -> Linear(8,1) -> tanh on cat(wdl, plys)
+        sd["value_head.body_final.0.weight"] = (rng.standard_normal((8, 4)) * 0.6).astype(np.float32)
+        sd["value_head.body_final.0.bias"] = (0.2 * rng.standard_normal(8)).astype(np.float32)
+        sd["value_head.body_final.2.weight"] = (rng.standard_normal((1, 8)) * 0.3).astype(np.float32)
+        sd["value_head.body_final.2.bias"] = (0.1 * rng.standard_normal(1)).astype(np.float32)
+    else:
+        # in the "wdl" configuration these tensors exist in the state_dict but are never executed (builder_util.py:320-324)
+        sd["value_head.body_final.0.weight"] = (rng.standard_normal((fc, nf)) / np.sqrt(nf)).astype(np.float32)
+        sd["value_head.body_final.0.bias"] = (0.1 * rng.standard_normal(fc)).astype(np.float32)
+        sd["value_head.body_final.2.weight"] = (rng.standard_normal((1, fc)) / np.sqrt(fc)).astype(np.float32)
+        if vh == "tanh":   # keeps |value| spread ~0.2 so that fp16 weight rounding alone stays well inside the 1e-2 bar
+            sd["value_head.body_final.2.weight"] *= np.float32(0.5)
+        sd["value_head.body_final.2.bias"] = (0.1 * rng.standard_normal(1)).astype(np.float32)
     pc = spec["policy_channels"]
     if spec["arch"] == ARCH_CROSSBOARD_RISEV33:
         _random_crossboard(rng, spec, sd)
         return sd
-    sd["policy_heads.shared_body.0.weight"] = _conv(rng, (C, C, 3, 3))
-    _bn(rng, C, "policy_heads.shared_body.1", sd)
-    for b in range(2):
-        sd[f"policy_heads.board_projections.{b}.weight"] = _conv(rng, (pc, C, 3, 3), gain=1.2)
+    if spec.get("shared_policy_trunk", True):
+        sd["policy_heads.shared_body.0.weight"] = _conv(rng, (C, C, 3, 3))
+        _bn(rng, C, "policy_heads.shared_body.1", sd)
+        for b in range(2):
+            sd[f"policy_heads.board_projections.{b}.weight"] = _conv(rng, (pc, C, 3, 3), gain=1.2)
+    else:   # two _PolicyHead(384) (builder_util.py:206-243): conv3x3 + BN + act, conv3x3 -> 73 planes
+        for b in range(2):
+            sd[f"policy_heads.{b}.body.0.weight"] = _conv(rng, (C, C, 3, 3))
+            _bn(rng, C, f"policy_heads.{b}.body.1", sd)
+            sd[f"policy_heads.{b}.body.3.weight"] = _conv(rng, (pc, C, 3, 3), gain=1.2)
     return sd
 
 
@@ -171,9 +212,11 @@ def _fold(w: np.ndarray, sd, bn_prefix: str):
 
 
 def fold_state_dict(sd: Dict[str, np.ndarray], spec: dict | None = None) -> Dict[str, np.ndarray]:
-    """Reference state_dict -> the folded fp32 tensors of the .hvmw container."""
-    spec = spec or risev33_spec()
+    """Reference state_dict -> the folded fp32 tensors of the .hvmw container.  The head variants
+    (shared / per-board policy heads; WDL, MLP or tanh value head) are read off the key names, so the
+    container says by its tensor names what the evaluator has to run (csrc/hm_net.cu build_net)."""
     sd = {k: np.asarray(v) for k, v in sd.items()}
+    spec = spec or spec_from_state_dict(sd)
     out: Dict[str, np.ndarray] = {}
     out["stem.w"], out["stem.b"] = _fold(sd["body_spatial.0.body.0.weight"], sd, "body_spatial.0.body.1")
     for i, (k, cop, eca) in enumerate(zip(spec["kernels"], spec["cops"], spec["eca"])):
@@ -191,18 +234,37 @@ def fold_state_dict(sd: Dict[str, np.ndarray], spec: dict | None = None) -> Dict
             out[q + "eca.b"] = sd[p + "se.body.0.bias"].astype(np.float32)
     w, b = _fold(sd["value_head.body.0.weight"], sd, "value_head.body.1")
     out["value.conv.w"], out["value.conv.b"] = w.reshape(w.shape[0], -1), b
-    out["value.wdl.w"] = sd["value_head.body_wdl.0.weight"].astype(np.float32)
-    out["value.wdl.b"] = sd["value_head.body_wdl.0.bias"].astype(np.float32)
-    out["value.plys.w"] = sd["value_head.body_plys.0.weight"].astype(np.float32)
-    out["value.plys.b"] = sd["value_head.body_plys.0.bias"].astype(np.float32)
+    f32 = np.float32
+    if "value_head.body_wdl.0.weight" in sd:
+        out["value.wdl.w"] = sd["value_head.body_wdl.0.weight"].astype(f32)
+        out["value.wdl.b"] = sd["value_head.body_wdl.0.bias"].astype(f32)
+        out["value.plys.w"] = sd["value_head.body_plys.0.weight"].astype(f32)
+        out["value.plys.b"] = sd["value_head.body_plys.0.bias"].astype(f32)
+        if tuple(sd["value_head.body_final.0.weight"].shape) == (8, 4):   # use_mlp_wdl_ply
+            out["value.mlp0.w"] = sd["value_head.body_final.0.weight"].astype(f32)
+            out["value.mlp0.b"] = sd["value_head.body_final.0.bias"].astype(f32)
+            out["value.mlp2.w"] = sd["value_head.body_final.2.weight"].astype(f32)
+            out["value.mlp2.b"] = sd["value_head.body_final.2.bias"].astype(f32)
+        # else: body_final exists in the state_dict but is never executed (builder_util.py:320-324)
+    else:   # tanh value head (builder_util.py:297-301, :326)
+        out["value.final0.w"] = sd["value_head.body_final.0.weight"].astype(f32)
+        out["value.final0.b"] = sd["value_head.body_final.0.bias"].astype(f32)
+        out["value.final2.w"] = sd["value_head.body_final.2.weight"].astype(f32)
+        out["value.final2.b"] = sd["value_head.body_final.2.bias"].astype(f32)
     if spec["arch"] == ARCH_CROSSBOARD_RISEV33:
         _fold_crossboard(sd, spec, out)
         return out
-    out["policy.shared.w"], out["policy.shared.b"] = _fold(
-        sd["policy_heads.shared_body.0.weight"], sd, "policy_heads.shared_body.1"
-    )
-    out["policy.a.w"] = sd["policy_heads.board_projections.0.weight"].astype(np.float32)
-    out["policy.b.w"] = sd["policy_heads.board_projections.1.weight"].astype(np.float32)
+    if "policy_heads.shared_body.0.weight" in sd:
+        out["policy.shared.w"], out["policy.shared.b"] = _fold(
+            sd["policy_heads.shared_body.0.weight"], sd, "policy_heads.shared_body.1"
+        )
+        out["policy.a.w"] = sd["policy_heads.board_projections.0.weight"].astype(f32)
+        out["policy.b.w"] = sd["policy_heads.board_projections.1.weight"].astype(f32)
+    else:   # per-board _PolicyHead(384): same tensor names as the crossboard per-board heads
+        for b in range(2):
+            w, bias = _fold(sd[f"policy_heads.{b}.body.0.weight"], sd, f"policy_heads.{b}.body.1")
+            out[f"pol{b}.c1.w"], out[f"pol{b}.c1.b"] = w, bias
+            out[f"pol{b}.c2.w"] = sd[f"policy_heads.{b}.body.3.weight"].astype(f32)
     return out
 
 
@@ -285,9 +347,9 @@ def read_hvmw(raw_or_path) -> Dict[str, np.ndarray]:
     return out
 
 
-def random_hvmw(seed: int = 0, path=None, arch: int = ARCH_RISEV33) -> bytes:
+def random_hvmw(seed: int = 0, path=None, arch: int = ARCH_RISEV33, spec: dict | None = None) -> bytes:
     """Seeded random-init weights as an .hvmw blob (what bench.py loads)."""
-    spec = spec_for_arch(arch)
+    spec = spec or spec_for_arch(arch)
     return write_hvmw(path, fold_state_dict(random_state_dict(spec, seed), spec), spec["arch"])
 
 
@@ -306,11 +368,14 @@ def convert_checkpoint(src: str, dst: str) -> Dict[str, np.ndarray]:
             if k.startswith(prefix):
                 k = k[len(prefix):]
         clean[k] = v.detach().to(torch.float32).cpu().numpy()
-    spec = risev33_spec()
+    # the architecture and its head variants are read off the checkpoint's own keys: crossboard-risev33 has
+    # cross_board_blocks.*, per-board policy heads have policy_heads.{0,1}.body.*, a tanh value head has no body_wdl
+    spec = spec_from_state_dict(clean)
     want = random_state_dict(spec, seed=0)
     missing = sorted(set(want) - set(clean))
     if missing:
-        raise KeyError(f"checkpoint lacks {len(missing)} tensors of risev33, e.g. {missing[:3]}")
+        name = "crossboard-risev33" if spec["arch"] == ARCH_CROSSBOARD_RISEV33 else "risev33"
+        raise KeyError(f"checkpoint lacks {len(missing)} tensors of {name}, e.g. {missing[:3]}")
     bad = [k for k in want if tuple(clean[k].shape) != tuple(want[k].shape)]
     if bad:
         raise ValueError(f"shape mismatch for {bad[:3]}")

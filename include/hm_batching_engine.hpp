@@ -37,13 +37,19 @@ namespace hm {
 class BatchingBackend {
 public:
     // One backend per device for the whole process (created on first use).
+    // The registry is a deliberately leaked singleton: the backends own CUDA resources (an hm_engine, pinned
+    // staging) and dispatcher threads, and destroying those from a static destructor would run after the CUDA
+    // runtime may already be gone.  shutdownAll() tears them down explicitly where a process wants that.
     static BatchingBackend& forDevice(int device, int smallBatch) {
-        static std::mutex mu;
-        static std::map<int, std::unique_ptr<BatchingBackend>> all;
-        std::lock_guard<std::mutex> lock(mu);
-        auto& slot = all[device];
-        if (!slot) slot.reset(new BatchingBackend(device, smallBatch));
+        std::lock_guard<std::mutex> lock(registryMutex());
+        auto& slot = registry()[device];
+        if (!slot) slot = new BatchingBackend(device, smallBatch);
         return *slot;
+    }
+    static void shutdownAll() {
+        std::lock_guard<std::mutex> lock(registryMutex());
+        for (auto& kv : registry()) delete kv.second;
+        registry().clear();
     }
 
     bool load(const std::string& path) {
@@ -60,15 +66,34 @@ public:
     long passes() const { return m_passes.load(); }
     long rowsServed() const { return m_rowsServed.load(); }
 
-    // -> slot id or -1 when all slots of the device are taken
+    // -> slot id or -1 when all slots of the device are taken.  Slots given back by releaseSlot are reused first.
     int acquireSlot() {
         std::lock_guard<std::mutex> lock(m_slotMutex);
-        if (m_nextSlot >= slotsTotal()) return -1;
-        const int id = m_nextSlot++;
+        int id;
+        if (!m_freeSlots.empty()) {
+            id = m_freeSlots.back();
+            m_freeSlots.pop_back();
+        } else {
+            if (m_nextSlot >= slotsTotal()) return -1;
+            id = m_nextSlot++;
+        }
         Group& g = m_groups[id % kGroups];
         std::lock_guard<std::mutex> gl(g.mutex);
         ++g.active;
         return id;
+    }
+    // Gives a slot back (engine destroyed / game finished): the group no longer waits for it when it decides whether
+    // a pass is full, and a later engine can take it.  The slot must be idle (no request in flight).
+    void releaseSlot(int id) {
+        if (id < 0) return;
+        std::lock_guard<std::mutex> lock(m_slotMutex);
+        Group& g = m_groups[id % kGroups];
+        {
+            std::lock_guard<std::mutex> gl(g.mutex);
+            if (g.active > 0) --g.active;
+        }
+        g.wake.notify_one();   // pending >= active may have become true
+        m_freeSlots.push_back(id);
     }
 
     bool enqueue(int slot, const uint16_t* obs) {
@@ -193,7 +218,11 @@ private:
     bool m_loaded = false;
     std::string m_path;
     int m_nextSlot = 0;
+    std::vector<int> m_freeSlots;
     std::atomic<long> m_passes{0}, m_rowsServed{0};
+
+    static std::mutex& registryMutex() { static std::mutex* mu = new std::mutex; return *mu; }
+    static std::map<int, BatchingBackend*>& registry() { static auto* all = new std::map<int, BatchingBackend*>; return *all; }
 };
 
 // The reference's Engine surface (nn/engine.h:43-132) for a small batch, served by the device's
@@ -213,6 +242,9 @@ public:
           m_workers(HM_DEFAULT_WORKERS) {}
     BatchingEngine(const BatchingEngine&) = delete;
     BatchingEngine& operator=(const BatchingEngine&) = delete;
+    ~BatchingEngine() {   // hand the large-batch slots of this engine's workers back to the device backend
+        for (Worker& w : m_workers) m_backend.releaseSlot(w.slot);
+    }
 
     bool loadNetwork(const std::string& onnxFile, const std::string& engineFile = std::string()) {
         (void)engineFile;

@@ -154,7 +154,9 @@ int hm_engine_enqueue_positions(hm_engine* e, const hm_packed_pos* pos, size_t n
 int hm_engine_sync_priors(hm_engine* e, size_t worker, const float** priors,
                           const float** values, const float** raw);
 
-void hm_engine_set_value_config(hm_engine* e, const hm_value_config* cfg);
+/* Runtime configuration of the value shaping (SearchParams::RuntimeConfig fields of search_params.h:275-295 read by
+ * searchthread.cc:569-619).  Returns 0 (and changes nothing) while any worker has a request in flight. */
+int hm_engine_set_value_config(hm_engine* e, const hm_value_config* cfg);
 
 /* ---- root policy on the device: temperature, Dirichlet noise, joint-action sampling ---- */
 

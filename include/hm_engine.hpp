@@ -167,8 +167,8 @@ public:
     static void commitRootDraw(URNG& randomEngine, int32_t status) {
         if (status == HM_ROOT_RESAMPLED) (void)canonical(randomEngine);
     }
-    void setValueConfig(const hm_value_config& cfg) {
-        if (m_handle != nullptr) hm_engine_set_value_config(m_handle, &cfg);
+    bool setValueConfig(const hm_value_config& cfg) {   // false while a request is in flight
+        return m_handle != nullptr && hm_engine_set_value_config(m_handle, &cfg) != 0;
     }
     hm_engine* handle() const { return m_handle; }
     int getDeviceId() const { return m_deviceId; }

@@ -75,15 +75,27 @@ class ForwardOracle:
         v = F.relu(F.conv2d(x, t["value.conv.w"][:, :, None, None], t["value.conv.b"]))
         inter["value_feat"] = v
         flat = v.reshape(v.shape[0], -1)
-        wdl = F.linear(flat, t["value.wdl.w"], t["value.wdl.b"])
-        plys = torch.sigmoid(F.linear(flat, t["value.plys.w"], t["value.plys.b"]))
-        sm = torch.softmax(wdl, dim=1)
-        value = sm[:, 2] - sm[:, 0]
-        if cross:
-            # per-board _PolicyHead(192) on that board's map (rise_mobile_v3.py:336-347, builder_util.py:206-243)
+        if "value.wdl.w" in t:
+            wdl = F.linear(flat, t["value.wdl.w"], t["value.wdl.b"])
+            plys = torch.sigmoid(F.linear(flat, t["value.plys.w"], t["value.plys.b"]))
+            if "value.mlp0.w" in t:   # use_mlp_wdl_ply (builder_util.py:292-296, :317-319)
+                hid = F.relu(F.linear(torch.cat((wdl, plys), dim=1), t["value.mlp0.w"], t["value.mlp0.b"]))
+                value = torch.tanh(F.linear(hid, t["value.mlp2.w"], t["value.mlp2.b"]))[:, 0]
+            else:
+                sm = torch.softmax(wdl, dim=1)
+                value = sm[:, 2] - sm[:, 0]
+        else:   # tanh value head (builder_util.py:297-301, :326); no auxiliary heads: the evaluator reports
+            # NaN wdl logits (searchthread.cc:581-583 then keeps the scalar value) and moves_left 0
+            hid = F.relu(F.linear(flat, t["value.final0.w"], t["value.final0.b"]))
+            value = torch.tanh(F.linear(hid, t["value.final2.w"], t["value.final2.b"]))[:, 0]
+            wdl = torch.full((x.shape[0], 3), float("nan"))
+            plys = torch.zeros((x.shape[0], 1))
+        if cross or "pol0.c1.w" in t:
+            # per-board _PolicyHead on that board's map (crossboard: rise_mobile_v3.py:336-347) or on the shared trunk
+            # (risev33 with shared_policy_trunk=False: rise_mobile_v3.py:198-204, builder_util.py:206-243, :393-396)
             pis = []
             for b in range(2):
-                s = F.relu(F.conv2d(maps[b], t[f"pol{b}.c1.w"], t[f"pol{b}.c1.b"], padding=1))
+                s = F.relu(F.conv2d(maps[b] if cross else x, t[f"pol{b}.c1.w"], t[f"pol{b}.c1.b"], padding=1))
                 inter[f"policy_c1_{b}"] = s
                 pis.append(F.conv2d(s, t[f"pol{b}.c2.w"], None, padding=1).reshape(x.shape[0], -1))
             pi_a, pi_b = pis
@@ -149,6 +161,62 @@ class ForwardOracle:
         return [tk.transpose(1, 2).reshape(B, D, 8, 8) for tk in toks]
 
 
+def deployed_precision_state_dict(sd: Dict[str, np.ndarray], spec: dict) -> Dict[str, np.ndarray]:
+    """The reference state_dict with every tensor-core operand weight at the precision the evaluator (and the
+    reference's own fp16 TensorRT plan, engine/src/nn/engine.cc:331-354) deploys: BatchNorm is folded into the
+    preceding conv in fp32 (hivemind_b200.weights.fold_state_dict), the folded conv / Linear weight is rounded to
+    fp16, and the pair is written back as conv.weight = rounded weight, BN = identity scale + the folded bias
+    (mean 0, var 1 - eps, gamma 1, beta = bias), so that the UNMODIFIED reference module computes
+    conv_fp16w(x) + bias in fp32 arithmetic.  Depthwise taps, biases, LayerNorms, embeddings and the value-head
+    Linears stay fp32, as on the device."""
+    from hivemind_b200 import weights as W
+
+    def r16(a):
+        return np.asarray(a, np.float32).astype(np.float16).astype(np.float32)
+
+    out = {k: np.array(v, copy=True) for k, v in sd.items()}
+
+    def requant(conv_key, bn_prefix):
+        w, b = W._fold(np.asarray(sd[conv_key]), sd, bn_prefix)
+        out[conv_key] = r16(w)
+        c = w.shape[0]
+        out[bn_prefix + ".weight"] = np.ones(c, np.float32)
+        out[bn_prefix + ".bias"] = b
+        out[bn_prefix + ".running_mean"] = np.zeros(c, np.float32)
+        out[bn_prefix + ".running_var"] = np.full(c, 1.0 - W.BN_EPS, np.float32)
+
+    requant("body_spatial.0.body.0.weight", "body_spatial.0.body.1")
+    for i, eca in enumerate(spec["eca"]):
+        p = f"body_spatial.{i + 1}."
+        requant(p + "body.0.weight", p + "body.1")
+        requant(p + "body.6.weight", p + "body.7")
+        if eca:
+            out[p + "se.body.0.weight"] = r16(sd[p + "se.body.0.weight"])
+    requant("value_head.body.0.weight", "value_head.body.1")
+    if "policy_heads.shared_body.0.weight" in sd:
+        requant("policy_heads.shared_body.0.weight", "policy_heads.shared_body.1")
+        for b in range(2):
+            k = f"policy_heads.board_projections.{b}.weight"
+            out[k] = r16(sd[k])
+    else:
+        for b in range(2):
+            requant(f"policy_heads.{b}.body.0.weight", f"policy_heads.{b}.body.1")
+            out[f"policy_heads.{b}.body.3.weight"] = r16(sd[f"policy_heads.{b}.body.3.weight"])
+    if spec["arch"] == W.ARCH_CROSSBOARD_RISEV33:
+        C = spec["channels"]
+        for b in range(2):
+            requant(f"board_token_projections.{b}.0.weight", f"board_token_projections.{b}.1")
+            # only the 384 trunk columns ride the tensor core; the 37 plane columns stay fp32 (token_embed_kernel)
+            w, _ = W._fold(np.asarray(sd[f"board_token_projections.{b}.0.weight"]), sd, f"board_token_projections.{b}.1")
+            out[f"board_token_projections.{b}.0.weight"][:, C:] = w[:, C:]
+        requant("value_fusion.0.weight", "value_fusion.1")
+        for l in range(spec["attention_layers"]):
+            p = f"cross_board_blocks.{l}."
+            for k in ("cross_attention.in_proj_weight", "cross_attention.out_proj.weight", "mlp.0.weight", "mlp.2.weight"):
+                out[p + k] = r16(sd[p + k])
+    return out
+
+
 def reference_model(state_dict: Dict[str, np.ndarray]):
     """Build the UNMODIFIED reference RiseV3 (needs /root/reference; this container only)
     and load `state_dict` strictly.  Returns an eval-mode torch module."""
@@ -164,15 +232,17 @@ def reference_model(state_dict: Dict[str, np.ndarray]):
             sys.path.insert(0, p)
     from src.architectures.rise_mobile_v3 import get_cross_board_rise_v33_model, get_rise_v33_model  # noqa: E402
 
-    class Args:  # src/training/train_loop.py:95-116 with use_wdl = use_plys_to_end = True
+    aux = "value_head.body_wdl.0.weight" in state_dict
+
+    class Args:  # src/training/train_loop.py:95-116; the head switches follow the keys of `state_dict`
         input_shape = (74, 8, 8)
         n_labels = 0
         channels_policy_head = 73
         select_policy_from_plane = True
-        use_wdl = True
-        use_plys_to_end = True
-        use_mlp_wdl_ply = False
-        shared_policy_trunk = True
+        use_wdl = aux
+        use_plys_to_end = aux
+        use_mlp_wdl_ply = aux and tuple(np.shape(state_dict["value_head.body_final.0.weight"])) == (8, 4)
+        shared_policy_trunk = "policy_heads.shared_body.0.weight" in state_dict
 
     if "cross_board_blocks.0.query_norm.weight" in state_dict:
         model = get_cross_board_rise_v33_model(Args()).eval()  # forces shared_policy_trunk=False itself (:286-290)
@@ -184,7 +254,13 @@ def reference_model(state_dict: Dict[str, np.ndarray]):
 
 @torch.no_grad()
 def reference_forward(model, planes: np.ndarray):
-    value, (pi_a, pi_b), _aux, wdl, plys = model(_t(planes))
+    out = model(_t(planes))
+    if len(out) == 2:   # no auxiliary heads (builder_util.py:403-406): tanh value only
+        value, (pi_a, pi_b) = out
+        n = value.shape[0]
+        return {"value": value[:, 0].numpy(), "wdl": np.full((n, 3), np.nan, np.float32),
+                "moves_left": np.zeros(n, np.float32), "pi_a": pi_a.numpy(), "pi_b": pi_b.numpy()}
+    value, (pi_a, pi_b), _aux, wdl, plys = out
     return {
         "value": value[:, 0].numpy(),
         "wdl": wdl.numpy(),

@@ -18,7 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 from hivemind_b200 import weights as W  # noqa: E402
-from oracle.forward_oracle import reference_forward, reference_model  # noqa: E402
+from oracle.forward_oracle import deployed_precision_state_dict, reference_forward, reference_model  # noqa: E402
 from oracle.pyoracle import POS_DTYPE, Ref, gen_config1  # noqa: E402
 
 GOLD = os.path.join(ROOT, "tests", "golden")
@@ -89,8 +89,14 @@ def main():
                 all_moves.append(m)
                 all_stm.append(b.stm_black(bn))
                 all_idx.append(ref.policy_index(m, b.stm_black(bn)))
-    np.savez_compressed(
-        os.path.join(GOLD, "positions_seed1234_n256.npz"),
+    regen = "--all" in sys.argv   # committed fixtures are rewritten only on request (python oracle/make_golden.py --all)
+
+    def save(fname, **arrays):
+        if regen or not os.path.exists(os.path.join(GOLD, fname)):
+            np.savez_compressed(os.path.join(GOLD, fname), **arrays)
+
+    save(
+        "positions_seed1234_n256.npz",
         packed=packed.view(np.uint8).reshape(N, 256), moves=moves, offsets=offsets,
         planes_f32=planes_f32, planes_f16=planes_f16, planes_u8=planes_u8,
         priors_formula_f16=priors, policy_index=indices, stm_black=stm,
@@ -98,7 +104,7 @@ def main():
         all_idx=np.array(all_idx, np.int32),
     )
     normal, drop = ref.policy_tables()
-    np.savez_compressed(os.path.join(GOLD, "policy_tables.npz"), normal=normal.astype(np.int16), drop=drop.astype(np.int16))
+    save("policy_tables.npz", normal=normal.astype(np.int16), drop=drop.astype(np.int16))
 
     # ---- reference known-answer positions -----------------------------------------------
     kat = {}
@@ -111,29 +117,46 @@ def main():
             kat[name + f".actions{bn}"] = acts
             kat[name + f".stm{bn}"] = np.array(b.stm_black(bn), np.uint8)
             kat[name + f".uci{bn}"] = np.array([b.move_uci(bn, m) for m in acts])
-    np.savez_compressed(os.path.join(GOLD, "reference_kat.npz"), **kat)
+    save("reference_kat.npz", **kat)
 
     # ---- stages F and X: reference PyTorch forward on seeded weights -------------------------
-    for spec, fname in ((W.risev33_spec(), "forward_risev33.npz"), (W.crossboard_spec(), "forward_crossboard.npz")):
+    # forward_<name>.npz: the UNMODIFIED reference module in fp32.  forward_<name>_fp16w.npz: the same module with
+    # its tensor-core operand weights at the deployed precision (fp16, engine/src/nn/engine.cc:331-354;
+    # forward_oracle.deployed_precision_state_dict) and fp32 arithmetic — device minus THIS is kernel error alone
+    # (activation rounding, accumulation order), device minus the fp32 fixture adds the weight quantisation.
+    fixtures = (
+        (W.risev33_spec(), "forward_risev33", True),
+        (W.crossboard_spec(), "forward_crossboard", True),
+        (W.risev33_spec(shared_policy_trunk=False, value_head="mlp"), "forward_risev33_perboard_mlp", False),
+        (W.risev33_spec(value_head="tanh"), "forward_risev33_tanh", False),
+    )
+    for spec, name, with_deployed in fixtures:
         sd = W.random_state_dict(spec, WEIGHT_SEED)
-        model = reference_model(sd)
-        out = reference_forward(model, planes_f32)
-        legal_logits = np.zeros(moves.size, np.float32)
-        ref_priors = np.zeros(moves.size, np.float32)
-        for g, b in enumerate(boards):
-            for bn in range(2):
-                lo, hi = offsets[2 * g + bn], offsets[2 * g + bn + 1]
-                pol = out["pi_a" if bn == 0 else "pi_b"][g]
-                idx = indices[lo:hi]
-                legal_logits[lo:hi] = np.where(idx >= 0, pol[np.maximum(idx, 0)], -np.inf)
-                ref_priors[lo:hi] = b.priors_f32(bn, pol, moves[lo:hi])
-        np.savez_compressed(
-            os.path.join(GOLD, fname),
-            weight_seed=np.array(WEIGHT_SEED), value=out["value"], wdl=out["wdl"], moves_left=out["moves_left"],
-            legal_logits=legal_logits, priors_f32=ref_priors,
-            pi_a_first8=out["pi_a"][:8], pi_b_first8=out["pi_b"][:8],
-            param_count=np.array(sum(p.numel() for p in model.parameters())),
-        )
+        variants = [("", sd)]
+        if with_deployed:
+            variants.append(("_fp16w", deployed_precision_state_dict(sd, spec)))
+        for suffix, state in variants:
+            fname = name + suffix + ".npz"
+            if os.path.exists(os.path.join(GOLD, fname)) and not regen:
+                continue
+            model = reference_model(state)
+            out = reference_forward(model, planes_f32)
+            legal_logits = np.zeros(moves.size, np.float32)
+            ref_priors = np.zeros(moves.size, np.float32)
+            for g, b in enumerate(boards):
+                for bn in range(2):
+                    lo, hi = offsets[2 * g + bn], offsets[2 * g + bn + 1]
+                    pol = out["pi_a" if bn == 0 else "pi_b"][g]
+                    idx = indices[lo:hi]
+                    legal_logits[lo:hi] = np.where(idx >= 0, pol[np.maximum(idx, 0)], -np.inf)
+                    ref_priors[lo:hi] = b.priors_f32(bn, pol, moves[lo:hi])
+            save(
+                fname,
+                weight_seed=np.array(WEIGHT_SEED), value=out["value"], wdl=out["wdl"], moves_left=out["moves_left"],
+                legal_logits=legal_logits, priors_f32=ref_priors,
+                pi_a_first8=out["pi_a"][:8], pi_b_first8=out["pi_b"][:8],
+                param_count=np.array(sum(p.numel() for p in model.parameters())),
+            )
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 

@@ -19,6 +19,8 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 ORACLE_SO = os.path.join(HERE, "liboracle.so")
 REF_SO = os.path.join(HERE, "_ref", "libhmref.so")
+REF_LEAFBATCH_SO = os.path.join(HERE, "_ref", "libhmref_leafbatch.so")  # reference Board + product LeafBatch harness
+REF_D5_SO = os.path.join(HERE, "_ref", "libhmref_d5.so")                # reference searchthread.cc on a scripted Engine
 
 NB_INPUT_VALUES = 4736
 NB_POLICY_VALUES = 4672
@@ -252,8 +254,25 @@ class Ref:
         L.hmref_dirichlet_mix.argtypes = [vp, vp, C.c_int, C.c_float]
         L.hmref_product_pack.argtypes = [vp, C.c_int, C.c_int, vp]
         L.hmref_product_actions.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_int]
-        L.hmref_leafbatch_run.argtypes = [C.c_int, vp, C.c_size_t, C.POINTER(vp), C.c_int, vp] + [vp] * 7 + [C.c_int]
         L.hmref_init()
+        self._leafbatch = None
+        self._d5 = None
+
+    def d5_shape(self, cases_u16, cfg=None) -> np.ndarray:
+        """The reference's OWN value shaping (searchthread.cc:569-621, compiled unmodified against a scripted Engine,
+        oracle/d5_pin.cc): cases_u16 [n,5] fp16 bit patterns (value, wdl loss/draw/win, moves_left) -> the value the
+        reference's one-leaf search backed up into the root."""
+        if self._d5 is None:
+            self._d5 = C.CDLL(REF_D5_SO)
+            self._d5.hmref_d5_shape.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_void_p]
+        cfg = cfg or ValueConfig.default()
+        cases = np.ascontiguousarray(cases_u16, np.uint16).reshape(-1, 5)
+        out = np.zeros(cases.shape[0], np.float32)
+        bad = self._d5.hmref_d5_shape(_ptr(cases), cases.shape[0], int(cfg.enable_wdl_eval), cfg.wdl_value_weight,
+                                      cfg.draw_contempt, cfg.moves_left_discount, _ptr(out))
+        if bad:
+            raise RuntimeError(f"{bad} one-leaf searches did not end with exactly one root visit")
+        return out
 
     # -- the product's include/hm_batch.hpp instantiated on the reference Board ----------
     def leafbatch_run(self, boards, blob: bytes, root=None, device: int = 0):
@@ -264,7 +283,11 @@ class Ref:
         offsets, priors = np.zeros(2 * n + 1, np.uint32), np.zeros(cap, np.float32)
         values, picks, status = np.zeros(n, np.float32), np.zeros((n, 2), np.uint32), np.zeros(n, np.int32)
         buf = C.create_string_buffer(blob, len(blob))
-        rc = self.lib.hmref_leafbatch_run(device, buf, len(blob), self.handles(boards), n,
+        if self._leafbatch is None:
+            vp = C.c_void_p
+            self._leafbatch = C.CDLL(REF_LEAFBATCH_SO)
+            self._leafbatch.hmref_leafbatch_run.argtypes = [C.c_int, vp, C.c_size_t, C.POINTER(vp), C.c_int, vp] + [vp] * 7 + [C.c_int]
+        rc = self._leafbatch.hmref_leafbatch_run(device, buf, len(blob), self.handles(boards), n,
                                           C.byref(root) if root is not None else None, _ptr(moves), _ptr(caps),
                                           _ptr(offsets), _ptr(priors), _ptr(values), _ptr(picks), _ptr(status), cap)
         if rc < 0:

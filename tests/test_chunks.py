@@ -158,6 +158,13 @@ def test_marginal_policy_matches_restated_reference():
         assert np.all(np.diff(gi.astype(np.int64)) > 0) and abs(float(gp.sum()) - 1.0) < 1e-5
     with pytest.raises(RuntimeError, match="no visited root edges"):
         chunks.marginal_policy([3, 4], [0, -1])
+    # a visited edge without a policy label is an error, as in the reference (selfplay.cc:392-398): the
+    # unrepresentable index -1 must never become label 65535, nor an index beyond the 4672 labels a target
+    for bad in (-1, 4672, 70000):
+        with pytest.raises(RuntimeError, match="absent from policy map"):
+            chunks.marginal_policy([3, bad], [5, 2])
+    gi, gp = chunks.marginal_policy([3, -1], [5, 0])   # ... but an UNVISITED unrepresentable edge is skipped like any other
+    assert gi.tolist() == [3] and gp.tolist() == [1.0]
 
 
 def test_quantisation_restated_matches_reference_fixture():

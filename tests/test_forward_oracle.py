@@ -10,7 +10,16 @@ import pytest
 N = 24  # positions: the torch fp32 CPU forward of these takes a few seconds
 
 
-@pytest.fixture(scope="module", params=["risev33", "crossboard"])
+SPECS = {
+    "risev33": lambda W: W.risev33_spec(),
+    "crossboard": lambda W: W.crossboard_spec(),
+    # the two other head configurations of the reference model (SURVEY.md §8a rows F5', F4 / §7 hard part 8)
+    "risev33_perboard_mlp": lambda W: W.risev33_spec(shared_policy_trunk=False, value_head="mlp"),
+    "risev33_tanh": lambda W: W.risev33_spec(value_head="tanh"),
+}
+
+
+@pytest.fixture(scope="module", params=list(SPECS))
 def arch(request):
     return request.param
 
@@ -26,7 +35,7 @@ def gold_forward(arch):  # overrides the session fixture: per architecture
 def folded_and_sd(arch):
     from hivemind_b200 import weights as W
 
-    spec = W.crossboard_spec() if arch == "crossboard" else W.risev33_spec()
+    spec = SPECS[arch](W)
     sd = W.random_state_dict(spec, seed=0)
     return W.fold_state_dict(sd, spec), sd
 
@@ -42,9 +51,11 @@ def oracle_out(oracle, gold_positions, folded_and_sd):
 def test_forward_oracle_matches_reference_golden_outputs(oracle_out, gold_forward, gold_positions):
     _, out = oracle_out
     assert int(gold_forward["weight_seed"]) == 0
-    assert int(gold_forward["param_count"]) in (14_122_085, 14_127_269)  # risev33, crossboard
+    # risev33 14,122,085 and crossboard 14,127,269; per-board heads add a second 384->384 conv + BN,
+    # the value MLP replaces the unused 1024-512-1 head; the tanh net has no WDL / plys Linears
+    assert int(gold_forward["param_count"]) in (14_122_085, 14_127_269, 14_924_693, 14_117_985)
     np.testing.assert_allclose(out["value"], gold_forward["value"][:N], atol=2e-5)
-    np.testing.assert_allclose(out["wdl"], gold_forward["wdl"][:N], atol=2e-4, rtol=1e-4)
+    np.testing.assert_allclose(out["wdl"], gold_forward["wdl"][:N], atol=2e-4, rtol=1e-4, equal_nan=True)
     np.testing.assert_allclose(out["moves_left"], gold_forward["moves_left"][:N], atol=2e-5)
     np.testing.assert_allclose(out["pi_a"][:8], gold_forward["pi_a_first8"], atol=5e-4, rtol=1e-4)
     np.testing.assert_allclose(out["pi_b"][:8], gold_forward["pi_b_first8"], atol=5e-4, rtol=1e-4)
@@ -73,4 +84,30 @@ def test_forward_oracle_matches_imported_reference_model(oracle_out, folded_and_
     planes, out = oracle_out
     ref = reference_forward(reference_model(folded_and_sd[1]), planes[:8])
     for k in ("value", "wdl", "moves_left", "pi_a", "pi_b"):
-        np.testing.assert_allclose(out[k][:8], ref[k], atol=5e-4, rtol=1e-4, err_msg=k)
+        np.testing.assert_allclose(out[k][:8], ref[k], atol=5e-4, rtol=1e-4, err_msg=k, equal_nan=True)
+
+
+@pytest.mark.parametrize("name", ["risev33", "crossboard"])
+def test_deployed_precision_fixture_is_the_oracle_on_fp16_rounded_weights(oracle, gold_positions, name):
+    """forward_<arch>_fp16w.npz came from the reference module with its tensor-core operand weights rounded to fp16
+    (forward_oracle.deployed_precision_state_dict); the oracle on the same rounding of the folded tensors agrees, and
+    the fixture differs from the fp32 one by the weight quantisation alone (a few 1e-3 on the value)."""
+    from conftest import GOLD
+    from hivemind_b200 import weights as W
+    from oracle.forward_oracle import ForwardOracle
+
+    spec = SPECS[name](W)
+    folded = W.fold_state_dict(W.random_state_dict(spec, seed=0), spec)
+    fp32_only = ("dw.w", "value.wdl.w", "value.plys.w", "pocket.w", "scalar.w", "qn.w", "mn.w", "ln.w")
+    q = {}
+    for k, v in folded.items():
+        mma = (k.endswith(".w") and not k.endswith(fp32_only)) or k.endswith(".wt")
+        q[k] = v.astype(np.float16).astype(np.float32) if mma else v
+    planes = oracle.encode_planes(gold_positions["packed"][:N], "f32")
+    out = ForwardOracle(q).forward(planes)
+    dep = dict(np.load(os.path.join(GOLD, f"forward_{name}_fp16w.npz")))
+    f32 = dict(np.load(os.path.join(GOLD, f"forward_{name}.npz")))
+    np.testing.assert_allclose(out["value"], dep["value"][:N], atol=5e-5)
+    np.testing.assert_allclose(out["moves_left"], dep["moves_left"][:N], atol=5e-5)
+    dq = np.abs(dep["value"] - f32["value"])
+    assert 1e-4 < dq.max() < 8e-3

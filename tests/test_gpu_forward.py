@@ -161,24 +161,57 @@ def test_batch_invariance_and_determinism(engine256, gold_positions):
     assert np.array_equal(c[2], a[2][perm])
 
 
-def test_full_size_batch512_properties(blob, gold_positions):
-    """BASELINE config 2 size: B = 512.  Size-independent properties: priors sum to 1, batch
-    halves agree with the 256-position run, values within [-1, 1]."""
+def _tile(g, reps):
+    """The 256 golden positions repeated `reps` times as one request (packed records, move lists, offsets)."""
+    pk = np.concatenate([g["packed"]] * reps)
+    mv = np.concatenate([g["moves"]] * reps)
+    total = int(g["offsets"][-1])
+    offs = np.concatenate([g["offsets"][:1]] + [g["offsets"][1:] + np.uint32(r * total) for r in range(reps)]).astype(np.uint32)
+    return pk, mv, offs
+
+
+def _assert_rows_match_golden(priors, raw, f, g, reps, value_tol, kl_tol, ml_tol):
+    """EVERY row of a tiled batch against the reference fixture (not 'the halves agree')."""
+    total = int(g["offsets"][-1])
+    for r in range(reps):
+        rows = slice(256 * r, 256 * (r + 1))
+        assert np.abs(raw[rows, 0] - f["value"]).max() <= value_tol, r
+        assert np.abs(raw[rows, 4] - f["moves_left"]).max() <= ml_tol, r
+        assert _max_kl(priors[r * total:(r + 1) * total], f["priors_f32"], g["offsets"]) <= kl_tol, r
+
+
+def test_full_size_batch512_matches_reference_golden(blob, gold_positions, gold_forward):
+    """BASELINE config 2 size, B = 512 (256 CTAs = 1.73 waves on 148 SMs, unlike the one-wave B = 256 engine):
+    every row against the reference PyTorch fixture at the north_star bars, on both execution slots."""
     from hivemind_b200.engine import Engine
 
     g = gold_positions
-    e = Engine(0, 512, 1)
+    e = Engine(0, 512, 2)
     assert e.loadNetworkFromMemory(blob)
-    pk = np.concatenate([g["packed"], g["packed"]])
-    mv = np.concatenate([g["moves"], g["moves"]])
-    offs = np.concatenate([g["offsets"], g["offsets"][1:] + g["offsets"][-1]]).astype(np.uint32)
-    priors, values, raw = e.evaluatePositions(pk, mv, offs)
-    n = g["moves"].size
-    assert np.array_equal(priors[:n], priors[n:]) and np.array_equal(raw[:256], raw[256:])
-    assert (np.abs(values) <= 1.0).all()
-    sums = np.add.reduceat(priors, offs[:-1].astype(np.int64))
-    assert np.allclose(sums, 1.0, atol=1e-5)
+    pk, mv, offs = _tile(g, 2)
+    for worker in (0, 1):
+        priors, values, raw = e.evaluatePositions(pk, mv, offs, worker)
+        _assert_rows_match_golden(priors, raw, gold_forward, g, 2, VALUE_TOL, KL_TOL, VALUE_TOL)
+        assert (np.abs(values) <= 1.0).all()
+        sums = np.add.reduceat(priors, offs[:-1].astype(np.int64))
+        assert np.allclose(sums, 1.0, atol=1e-5)
     e.close()
+
+
+def test_kernel_error_alone_vs_deployed_precision_reference(engine256, gold_positions):
+    """Against the reference module run with its tensor-core weights at the DEPLOYED precision (fp16,
+    engine/src/nn/engine.cc:331-354; tests/golden/forward_risev33_fp16w.npz): what is left is the kernels' own
+    error (fp16 activation storage, accumulation order) — bar 5e-3 on the value, half the north_star bar."""
+    import os
+
+    from conftest import GOLD
+
+    g = gold_positions
+    f = dict(np.load(os.path.join(GOLD, "forward_risev33_fp16w.npz")))
+    priors, values, raw = engine256.evaluatePositions(g["packed"], g["moves"], g["offsets"])
+    assert np.abs(raw[:, 0] - f["value"]).max() <= 5e-3
+    assert np.abs(raw[:, 4] - f["moves_left"]).max() <= 5e-3
+    assert _max_kl(priors, f["priors_f32"], g["offsets"]) <= KL_TOL / 2
 
 
 def test_load_errors_return_false(tmp_path):
@@ -191,6 +224,107 @@ def test_load_errors_return_false(tmp_path):
     assert not e.loadNetwork(str(bad), "")
     assert not e.enqueueInferenceHalf(np.zeros((8, 74, 8, 8), np.float16), 0)   # nothing loaded
     assert not e.synchronizeInferenceHalf(HalfInferenceOutputs(), 0)
+    # corrupt containers fail cleanly: a truncated blob, and a crafted entry whose offset + size wraps around 2^64
+    # (would pass a naive `off + nbytes > size` check and read far outside the blob)
+    import struct
+
+    from hivemind_b200 import weights as W
+
+    good = bytearray(W.write_hvmw(None, {"stem.w": np.zeros((4, 4), np.float32)}))
+    assert not e.loadNetworkFromMemory(bytes(good[: len(good) - 8]))
+    evil = bytearray(good)
+    struct.pack_into("<QQ", evil, 64 + 88, 2**64 - 4, 64)      # entry 0: offset, nbytes
+    assert not e.loadNetworkFromMemory(bytes(evil))
+    early = bytearray(good)
+    struct.pack_into("<QQ", early, 64 + 88, 0, 64)              # data may not overlap the header / table
+    assert not e.loadNetworkFromMemory(bytes(early))
+    e.close()
+
+
+def test_onnx_path_maps_to_a_fresh_sibling_hvmw(tmp_path, blob):
+    """loadNetwork("x.onnx") loads x.hvmw (the reference's call sites pass the ONNX path); an .onnx re-exported
+    AFTER the conversion is refused instead of silently playing the old network."""
+    import os
+
+    from hivemind_b200 import _lib
+    from hivemind_b200.engine import Engine
+
+    e = Engine(0, 8, 1)
+    hv, onnx = tmp_path / "net.hvmw", tmp_path / "net.onnx"
+    hv.write_bytes(blob)
+    assert e.loadNetwork(str(onnx), "")            # no .onnx file at all: the sibling is what there is
+    onnx.write_bytes(b"onnx export")
+    os.utime(onnx, (1_000_000_000, 1_000_000_000))  # older than the .hvmw
+    assert e.loadNetwork(str(onnx), "")
+    os.utime(onnx, None)
+    os.utime(hv, (1_000_000_000, 1_000_000_000))    # now the export is newer than the conversion
+    assert not e.loadNetwork(str(onnx), "")
+    assert "older than" in _lib.last_error()
+    e.close()
+
+
+def test_value_config_changes_without_rebuilding_workers(engine256, oracle, gold_positions):
+    """hm_engine_set_value_config: refused while a request is in flight, otherwise a device-side copy — pinned
+    output pointers handed out earlier stay valid and the next request is shaped under the new settings."""
+    from oracle.pyoracle import ValueConfig
+
+    g = gold_positions
+    e = engine256
+    priors, values, raw = e.evaluatePositions(g["packed"], g["moves"], g["offsets"])
+    before = values.copy()
+    assert e.enqueuePositions(g["packed"], g["moves"], g["offsets"], 1)
+    assert not e.setValueConfig(True, 1.0, 0.0, 0.1)             # worker 1 busy
+    assert e.synchronizePriors(1) is not None
+    try:
+        assert e.setValueConfig(True, 1.0, 0.0, 0.1)
+        assert np.array_equal(values, before)                    # the earlier pinned view is untouched
+        _, v2, raw2 = e.evaluatePositions(g["packed"], g["moves"], g["offsets"])
+        cfg = ValueConfig(1, 1.0, 0.0, 0.1)
+        want = np.array([oracle.shape_value(r[0], r[1:4], r[4], cfg) for r in raw2], np.float32)
+        assert np.allclose(v2, want, atol=2e-7, rtol=0)
+        assert np.abs(v2 - before).max() > 1e-3
+    finally:
+        assert e.setValueConfig()
+
+
+@pytest.mark.parametrize("name", ["risev33_perboard_mlp", "risev33_tanh"])
+def test_head_variants_match_reference_model(name, oracle, gold_positions):
+    """The reference model's other head configurations (SURVEY.md §8a F5' / F4, §7 hard part 8): two independent
+    _PolicyHead(384) (shared_policy_trunk=False, rise_mobile_v3.py:198-204) with the value MLP on cat(wdl, plys)
+    (use_mlp_wdl_ply, builder_util.py:292-296), and the tanh value head of nets built without auxiliary heads
+    (builder_util.py:297-301, :326).  Goldens from the reference PyTorch module (oracle/make_golden.py)."""
+    import os
+
+    from conftest import GOLD
+    from hivemind_b200 import weights as W
+    from hivemind_b200.engine import Engine, HalfInferenceOutputs
+
+    spec = (W.risev33_spec(shared_policy_trunk=False, value_head="mlp") if name == "risev33_perboard_mlp"
+            else W.risev33_spec(value_head="tanh"))
+    g = gold_positions
+    f = dict(np.load(os.path.join(GOLD, f"forward_{name}.npz")))
+    e = Engine(0, 256, 1)
+    assert e.loadNetworkFromMemory(W.random_hvmw(seed=0, spec=spec))
+    priors, values, raw = e.evaluatePositions(g["packed"], g["moves"], g["offsets"])
+    assert np.abs(raw[:, 0] - f["value"]).max() <= VALUE_TOL
+    assert _max_kl(priors, f["priors_f32"], g["offsets"]) <= KL_TOL
+    if name == "risev33_tanh":
+        # no auxiliary heads: NaN WDL logits (the reference's shaping then keeps the scalar value,
+        # searchthread.cc:581-583) and moves_left 0 (no discount) -> shaped value == clamp(value)
+        assert np.isnan(raw[:, 1:4]).all() and (raw[:, 4] == 0).all()
+        assert np.array_equal(values, np.clip(raw[:, 0], -1.0, 1.0))
+    else:
+        assert np.abs(raw[:, 4] - f["moves_left"]).max() <= VALUE_TOL
+        assert np.abs(raw[:, 1:4] - f["wdl"]).max() <= 5e-2
+        want = np.array([oracle.shape_value(r[0], r[1:4], r[4]) for r in raw], np.float32)
+        assert np.allclose(values, want, atol=2e-7, rtol=0)
+    out = HalfInferenceOutputs()
+    assert e.runInferenceHalf(np.ascontiguousarray(g["planes_f16"]).view(np.float16), out)
+    assert np.abs(out.value.astype(np.float32) - f["value"]).max() <= VALUE_TOL
+    assert np.abs(out.policyA[:8].astype(np.float32) - f["pi_a_first8"]).max() <= 0.15
+    assert np.abs(out.policyB[:8].astype(np.float32) - f["pi_b_first8"]).max() <= 0.15
+    if name == "risev33_tanh":
+        assert np.isnan(out.wdl.astype(np.float32)).all() and (out.movesLeft.astype(np.float32) == 0).all()
     e.close()
 
 
@@ -250,20 +384,42 @@ def test_crossboard_fused_path_matches_reference_model(cross_engine, gold_positi
     res = cross_engine.evaluatePositions(g["packed"], g["moves"], g["offsets"])
     assert res is not None
     priors, values, raw = res
-    # Stated tolerance for this architecture at fp16: max |dvalue| <= 2e-2 (measured 1.2e-2), mean
-    # <= 2e-3.  The random-init crossboard heads amplify trunk perturbations more than the risev33
-    # heads do: rounding ONLY the trunk weights to fp16 (what the reference's own fp16 TensorRT
-    # plan does as well) already moves the fp32 model's value by 8e-3 on these positions, our
-    # heads add 2e-3 (tests/diag/diagnose_crossboard.py, DESIGN.md "Precision").  Policy stays far
-    # inside its bar (KL 3e-4 vs 1e-3).
+    # north_star bars, as stated: max |dvalue| <= 1e-2, KL <= 1e-3.  The trunk keeps its residual stream in fp32
+    # (TMEM accumulators), so what is left is dominated by the fp16 rounding of the WEIGHTS, which
+    # the reference's own fp16 TensorRT plan shares (see the deployed-precision test below).
     dv = np.abs(raw[:, 0] - f["value"])
-    assert dv.max() <= 2e-2 and dv.mean() <= 2e-3
-    # moves_left is not a north_star parity quantity: it enters the shaped value scaled by 0.005
-    # (searchthread.cc:610-612), so 2e-2 here moves the value by 1e-4 (measured 1.0e-2 after the
-    # two extra attention blocks on the fp16 residual stream)
-    assert np.abs(raw[:, 4] - f["moves_left"]).max() <= 2e-2
+    assert dv.max() <= VALUE_TOL and dv.mean() <= 2e-3
+    assert np.abs(raw[:, 4] - f["moves_left"]).max() <= 1.5e-2   # enters the shaped value scaled by 0.005 (searchthread.cc:610-612)
     assert np.abs(raw[:, 1:4] - f["wdl"]).max() <= 5e-2
     assert _max_kl(priors, f["priors_f32"], g["offsets"]) <= KL_TOL
+
+
+def test_crossboard_kernel_error_alone_vs_deployed_precision_reference(cross_engine, gold_positions):
+    """Device vs the reference CrossBoardRiseV3 module with fp16-rounded tensor-core weights
+    (tests/golden/forward_crossboard_fp16w.npz): kernel error separated from weight quantisation, bar 5e-3."""
+    import os
+
+    from conftest import GOLD
+
+    g = gold_positions
+    f = dict(np.load(os.path.join(GOLD, "forward_crossboard_fp16w.npz")))
+    priors, values, raw = cross_engine.evaluatePositions(g["packed"], g["moves"], g["offsets"])
+    assert np.abs(raw[:, 0] - f["value"]).max() <= 5e-3
+    assert _max_kl(priors, f["priors_f32"], g["offsets"]) <= KL_TOL / 2
+
+
+def test_crossboard_full_size_batch1024_matches_reference_golden(gold_positions, gold_cross):
+    """BASELINE config 4 size, B = 1024: every row of the tiled golden positions against the reference fixture."""
+    from hivemind_b200 import weights as W
+    from hivemind_b200.engine import Engine
+
+    g = gold_positions
+    e = Engine(0, 1024, 1)
+    assert e.loadNetworkFromMemory(W.random_hvmw(seed=0, arch=W.ARCH_CROSSBOARD_RISEV33))
+    pk, mv, offs = _tile(g, 4)
+    priors, values, raw = e.evaluatePositions(pk, mv, offs)
+    _assert_rows_match_golden(priors, raw, gold_cross, g, 4, VALUE_TOL, KL_TOL, 1.5e-2)
+    e.close()
 
 
 def test_crossboard_reference_shaped_half_path(cross_engine, oracle, gold_positions, gold_cross):
@@ -273,7 +429,7 @@ def test_crossboard_reference_shaped_half_path(cross_engine, oracle, gold_positi
     obs = oracle.encode_planes(g["packed"], "f16")
     out = HalfInferenceOutputs()
     assert cross_engine.runInferenceHalf(obs, out)
-    assert np.abs(out.value.astype(np.float32) - f["value"]).max() <= 2e-2
+    assert np.abs(out.value.astype(np.float32) - f["value"]).max() <= VALUE_TOL + 5e-4   # + fp16 rounding of the output
     assert np.abs(out.policyA[:8].astype(np.float32) - f["pi_a_first8"]).max() <= 0.1
     assert np.abs(out.policyB[:8].astype(np.float32) - f["pi_b_first8"]).max() <= 0.1
     assert cross_engine._L.hm_engine_arch(cross_engine._h) == 1

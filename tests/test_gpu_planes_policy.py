@@ -121,3 +121,26 @@ def test_value_shaping_matches_oracle(engine, oracle):
     want = np.array([oracle.shape_value_half(int(v), w, int(m)) for v, w, m in
                      zip(value.view(np.uint16), wdl.view(np.uint16), ml.view(np.uint16))], np.float32)
     assert np.allclose(got, want, rtol=0, atol=2e-7)
+
+
+def test_value_shaping_matches_the_reference_search(engine):
+    """D5 against the reference's own compiled SearchThread::process_batch (tests/golden/value_shaping.npz,
+    oracle/make_golden_d5.py): <= 1 ulp (the g++ reference build contracts one FMA), NaN where the reference has
+    NaN, every runtime configuration of the fixture through hm_engine_set_value_config."""
+    import os
+
+    from conftest import GOLD
+
+    g = np.load(os.path.join(GOLD, "value_shaping.npz"))
+    c = g["cases_u16"]
+    value, wdl, ml = c[:, 0].copy().view(np.float16), c[:, 1:4].copy().view(np.float16), c[:, 4].copy().view(np.float16)
+    try:
+        for i, (en, w, disc, contempt) in enumerate(g["configs"]):
+            engine.setValueConfig(bool(en), float(w), float(disc), float(contempt))
+            got = engine.shapeValuesHalf(value, wdl, ml)
+            want = g[f"shaped_{i}"]
+            assert np.array_equal(np.isnan(got), np.isnan(want)), i
+            m = ~np.isnan(want)
+            assert np.abs(got[m] - want[m]).max() <= 1.2e-7, i
+    finally:
+        engine.setValueConfig()

@@ -6,6 +6,7 @@ import ctypes as C
 import os
 import re
 import shutil
+import struct
 import subprocess
 import sys
 
@@ -189,6 +190,39 @@ def test_checkpoint_conversion_cli(tmp_path):
         W.convert_checkpoint(str(ck), str(out))
 
 
+def test_checkpoint_conversion_picks_the_architecture_from_the_keys(tmp_path):
+    """convert_checkpoint reads architecture and head variants off the checkpoint's own keys (crossboard-risev33 has
+    cross_board_blocks.*, per-board policy heads policy_heads.{0,1}.body.*, a tanh value head no body_wdl): every
+    variant round-trips checkpoint -> .hvmw -> read_hvmw -> ForwardOracle and gives the outputs of folding directly."""
+    import torch
+
+    from hivemind_b200 import weights as W
+    from oracle.forward_oracle import ForwardOracle
+
+    planes = np.load(os.path.join(ROOT, "tests", "golden", "positions_seed1234_n256.npz"))["planes_f32"][:2]
+    for spec in (W.crossboard_spec(), W.risev33_spec(shared_policy_trunk=False, value_head="mlp"),
+                 W.risev33_spec(value_head="tanh"), W.risev33_spec()):
+        sd = W.random_state_dict(spec, seed=3)
+        ck = tmp_path / "model.tar"
+        torch.save({"model_state_dict": {k: torch.from_numpy(v) for k, v in sd.items()}}, ck)
+        out = tmp_path / "net.hvmw"
+        folded = W.convert_checkpoint(str(ck), str(out))
+        raw = out.read_bytes()
+        assert struct.unpack_from("<I", raw, 8)[0] == spec["arch"]
+        back = W.read_hvmw(raw)
+        assert set(back) == set(folded) and all(np.array_equal(back[k], folded[k]) for k in back)
+        a = ForwardOracle(back).forward(planes)
+        b = ForwardOracle(W.fold_state_dict(sd, spec)).forward(planes)
+        assert all(np.array_equal(a[k], b[k], equal_nan=True) for k in a)
+        assert W.spec_from_state_dict(sd) == spec
+    # a crossboard checkpoint that lost its attention output projection is named as such
+    sd = W.random_state_dict(W.crossboard_spec(), seed=3)
+    sd.pop("cross_board_blocks.1.cross_attention.out_proj.weight")
+    torch.save({k: torch.from_numpy(v) for k, v in sd.items()}, ck)
+    with pytest.raises(KeyError, match="crossboard-risev33"):
+        W.convert_checkpoint(str(ck), str(out))
+
+
 @pytest.mark.skipif(shutil.which("g++") is None, reason="no g++")
 def test_batching_engine_header_compiles_alone_and_fails_loudly_without_gpu(tmp_path):
     """include/hm_batching_engine.hpp needs nothing of the reference; without a CUDA device loadNetwork and the
@@ -205,6 +239,17 @@ def test_batching_engine_header_compiles_alone_and_fails_loudly_without_gpu(tmp_
 #include "hm_batching_engine.hpp"
 int main() {
     hm::BatchingEngine a(0, 8), b(0, 8);
+    // slots are handed back when an engine dies: far more engines than slots may exist over a process lifetime
+    {
+        std::vector<int> taken;
+        hm::BatchingBackend& be = a.backend();
+        for (int round = 0; round < 3; ++round) {
+            for (int i = 0; i < be.slotsTotal(); ++i) { const int s = be.acquireSlot(); if (s < 0) return 3; taken.push_back(s); }
+            if (be.acquireSlot() != -1) return 4;
+            for (int s : taken) be.releaseSlot(s);
+            taken.clear();
+        }
+    }
     const bool loaded = a.loadNetwork("/nonexistent/model.hvmw", "");
     std::vector<__half> obs(8 * HM_NB_INPUT_VALUES);
     hm::BatchingEngine::HalfInferenceOutputs out;

@@ -2,6 +2,7 @@
 reference itself (oracle/make_golden.py) and against the reference's known-answer tests
 (engine/tests/test_move_gen.cc, cited per test)."""
 import numpy as np
+import pytest
 
 from conftest import formula_logits
 from oracle.pyoracle import POS_DTYPE, ValueConfig
@@ -136,6 +137,49 @@ def test_kat_fast_index_matches_label_lookup(oracle, gold_kat):  # test_move_gen
 
 
 # ---- value shaping (searchthread.cc:569-619) --------------------------------------------
+
+def _same_shaped(got, want):
+    """Within 1 ulp of the reference build (g++ -O2 -march=x86-64-v3 contracts `(1-w)*s + w*v` into an FMA,
+    the restatement rounds both products); NaN exactly where the reference has NaN; the sign of a zero is not
+    part of the fixture (it is read back as 0.0f + value from the root's value sum)."""
+    got, want = np.asarray(got, np.float32), np.asarray(want, np.float32)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    m = ~np.isnan(want)
+    assert np.abs(got[m] - want[m]).max() <= 1.2e-7
+
+
+def test_value_shaping_pinned_by_the_reference_search(oracle):
+    """tests/golden/value_shaping.npz = what the reference's OWN SearchThread::process_batch
+    (searchthread.cc:569-621, compiled unmodified against a scripted Engine, oracle/d5_pin.cc) backed up for
+    344 fp16 (value, wdl, moves_left) inputs incl. non-finite ones under 5 runtime configurations."""
+    import os
+
+    from conftest import GOLD
+
+    g = np.load(os.path.join(GOLD, "value_shaping.npz"))
+    cases = g["cases_u16"]
+    assert cases.shape[0] >= 256
+    for i, (en, w, disc, contempt) in enumerate(g["configs"]):
+        cfg = ValueConfig(int(en), float(w), float(disc), float(contempt))
+        got = [oracle.shape_value_half(int(r[0]), r[1:4], int(r[4]), cfg) for r in cases]
+        _same_shaped(got, g[f"shaped_{i}"])
+
+
+def test_value_shaping_fixture_is_what_the_reference_computes(ref):
+    """Where the compiled reference exists: regenerate a slice of the fixture live."""
+    import os
+
+    from conftest import GOLD
+    from oracle.pyoracle import REF_D5_SO
+
+    if not os.path.exists(REF_D5_SO):
+        pytest.skip("oracle/_ref/libhmref_d5.so not built")
+    g = np.load(os.path.join(GOLD, "value_shaping.npz"))
+    for i in (0, 3):
+        en, w, disc, contempt = g["configs"][i]
+        live = ref.d5_shape(g["cases_u16"], ValueConfig(int(en), float(w), float(disc), float(contempt)))
+        assert np.array_equal(live.view(np.uint32), g[f"shaped_{i}"].view(np.uint32))
+
 
 def test_value_shaping_cases(oracle):
     cfg = ValueConfig.default()
