@@ -23,6 +23,9 @@ FLAGS = [
     "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC",
 ]
+# bring-up builds only, e.g. HM_EXTRA_NVCC_FLAGS=-DHM_BRINGUP (timeline tracing in trunk_kernel, tools/trace_trunk.py);
+# the default build carries no tracing or debug switches
+FLAGS += os.environ.get("HM_EXTRA_NVCC_FLAGS", "").split()
 
 
 def _deps():
@@ -39,10 +42,10 @@ def needs_build() -> bool:
     return any(os.path.getmtime(f) > t for f in _deps())
 
 
-def _compile(src: str) -> str:
+def _compile(src: str, force: bool = False) -> str:
     obj = os.path.join(OBJ, src + ".o")
     srcp = os.path.join(CSRC, src)
-    if os.path.exists(obj) and all(os.path.getmtime(f) <= os.path.getmtime(obj) for f in _deps()):
+    if not force and os.path.exists(obj) and all(os.path.getmtime(f) <= os.path.getmtime(obj) for f in _deps()):
         return obj
     cmd = [NVCC, *FLAGS, "-c", srcp, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -57,7 +60,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     sources = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     with ThreadPoolExecutor(max_workers=len(sources)) as ex:
-        objs = list(ex.map(_compile, sources))
+        objs = list(ex.map(lambda s: _compile(s, force), sources))
     # -Bsymbolic / --exclude-libs: keep our (possibly static) libstdc++ symbols private so
     # the library can be dlopen'ed into a process that already loaded another libstdc++.
     cmd = [NVCC, "-shared", "-o", OUT, *objs, "-cudart", "static",

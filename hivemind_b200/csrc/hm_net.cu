@@ -320,7 +320,15 @@ std::unique_ptr<Net> build_net(const HvmwBlob& blob) {
             pp[128 + r] = db->data[c];
             for (int t = 0; t < kk; ++t) pp[256 + t * 128 + r] = dw->data[c * kk + t];
         }
-        bias2.insert(bias2.end(), b2->data, b2->data + 384);
+        // The trunk kernel keeps the residual stream as an fp32 TMEM accumulator that is never cleared, so the pw2
+        // biases are carried as a CUMULATIVE vector added when the accumulator is read: the sum of the biases of all
+        // blocks since the stream was last written back with its bias included (the kernel start, or the ECA gate of
+        // a block, which stores g * (accumulator + cumulative bias) and so re-bases the sum to zero).
+        {
+            const bool rebased = net->blocks.empty() || T(p + "eca.w") != nullptr;
+            const size_t prev = net->blocks.empty() ? 0 : static_cast<size_t>(net->blocks.back().bias2_off);
+            for (int o = 0; o < 384; ++o) bias2.push_back(b2->data[o] + (rebased ? 0.0f : bias2[prev + o]));
+        }
         net->param_count += w1->numel() + b1->numel() + w2->numel() + b2->numel() + dw->numel() + db->numel();
         if (const HvmwTensor* ew = T(p + "eca.w")) {
             const HvmwTensor* eb = T(p + "eca.b");
@@ -495,6 +503,11 @@ struct TrunkRun {
     int grid;
 };
 bool trace_trunk_run(Worker& w, int run, unsigned long long* out_host, int* cap) {
+#ifndef HM_BRINGUP
+    (void)w; (void)run; (void)out_host; (void)cap;
+    set_error("timeline tracing is compiled out of this build (rebuild with -DHM_BRINGUP)");
+    return false;
+#else
     if (run < 0 || run >= static_cast<int>(w.trunk_runs.size())) { set_error("no such trunk run"); return false; }
     const size_t bytes = 3 * TR_TRACE_CAP * sizeof(unsigned long long);
     unsigned long long* d = nullptr;
@@ -502,13 +515,14 @@ bool trace_trunk_run(Worker& w, int run, unsigned long long* out_host, int* cap)
     cudaMemsetAsync(d, 0, bytes, w.stream);
     TrunkRun r = *w.trunk_runs[run];
     r.p.trace = d;
-    if (const char* dbg = getenv("HM_TRUNK_DBG")) r.p.dbg = atoi(dbg);
+    if (const char* dbg = getenv("HM_TRUNK_DBG")) r.p.dbg = atoi(dbg);   // bring-up builds, traced launches only
     trunk_kernel<<<r.grid, TR_THREADS, TR_SMEM, w.stream>>>(r.p, r.tm_x, r.tm_w1, r.tm_w2);
     bool ok = cuda_ok(cudaMemcpyAsync(out_host, d, bytes, cudaMemcpyDeviceToHost, w.stream), "D2H trace") &&
               cuda_ok(cudaStreamSynchronize(w.stream), "trace sync");
     cudaFree(d);
     if (cap) *cap = TR_TRACE_CAP;
     return ok;
+#endif
 }
 
 // A run of consecutive bottleneck blocks [first, last) as one trunk_kernel launch.
@@ -530,7 +544,6 @@ static bool add_trunk_run(Worker& w, std::vector<Op>& ops, const Net& net, int f
     p.bias2 = net.trunk_bias2;
     p.trace = nullptr;
     p.dbg = 0;
-    if (const char* dbg = getenv("HM_TRUNK_DBG")) p.dbg = atoi(dbg);  // timing experiments only (wrong results)
     const int grid = n_pos / 2;
     const CUtensorMap tw1 = net.tm_w1, tw2 = net.tm_w2;
     w.trunk_runs.push_back(std::make_shared<TrunkRun>(TrunkRun{p, tm_x, tw1, tw2, grid}));
@@ -844,8 +857,10 @@ static bool setup_worker(Engine* e, Worker& w) {
     auto& ops = w.ops_trunk;
     if (!add_dense(ops, net.stem, w.d_planes, HM_NB_INPUT_CHANNELS, B, w.d_trunk, true, false)) return false;
     int nblk = static_cast<int>(net.blocks.size());
-    if (const char* stop = getenv("HM_TRUNK_STOP"))  // debugging aid (tests/diag/diagnose.py): truncate the trunk
+#ifdef HM_BRINGUP
+    if (const char* stop = getenv("HM_TRUNK_STOP"))  // bring-up builds only (tests/diag/diagnose.py): truncate the trunk
         nblk = std::max(0, std::min(nblk, atoi(stop)));
+#endif
     // the whole trunk is ONE launch: ECA gates are computed inside the kernel (a gate depends on the
     // channel means of the SAME position only, builder_util.py:77-80)
     if (nblk > TR_MAX_BLOCKS) { set_error("trunks longer than TR_MAX_BLOCKS blocks are not supported"); return false; }
@@ -853,10 +868,6 @@ static bool setup_worker(Engine* e, Worker& w) {
     if (nblk > 0 && !add_trunk_run(w, ops, net, 0, nblk, w.d_trunk, B)) return false;
     w.debug_views["planes"] = {w.d_planes, {B, HM_NB_INPUT_VALUES, 0}};
     w.debug_views["trunk"] = {w.d_trunk, {B, 384 * 64, 0}};
-    {
-        void* clk = nullptr;
-        if (cudaGetSymbolAddress(&clk, g_trunk_clk) == cudaSuccess) w.debug_views["trunk_clk"] = {clk, {1, 16, 1}};
-    }
     const bool cross = net.arch == HM_ARCH_CROSSBOARD_RISEV33;
     act_t* tokens = nullptr;
     if (cross && !add_crossboard(w, ops, net, B, &tokens)) return false;

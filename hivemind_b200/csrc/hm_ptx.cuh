@@ -52,6 +52,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// non-blocking probe of a phase (try_wait may suspend the thread for a while; this never does): issue it early,
+// consume the result late, fall back to mbar_wait when it says "not yet"
+__device__ __forceinline__ uint32_t mbar_test_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
@@ -155,12 +168,54 @@ __device__ __forceinline__ void umma_f16_lh(uint32_t d_tmem, uint32_t a_lo, uint
         "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// EIGHT MMAs (two 16 KB A tiles x four K16 steps) and the two per-tile commits as ONE asm block: the descriptor
+// arithmetic sits between the MMAs instead of in front of the burst.  The tensor pipe queues only two or three MMAs
+// behind the running one (tools/probes/probe_issue.cu: a few extra instructions per burst already cost 8-10 % once
+// they are hoisted in front of it), so everything the issuing thread does between two bursts — barrier wait,
+// ~40 R2UR/UMOV of descriptor set-up — has to fit into ~150 cycles or the pipe starves; inside the block each MMA's
+// set-up runs while the queue is still full.  Descriptor low words: A tile j, step k = a_lo + j*1024 + 2k (16-byte
+// units); B = b_lo + j*BJ + k*BK.  acc_first: accumulate flag of the very first MMA (the others accumulate).
+template <int BJ, int BK>
+__device__ __forceinline__ void umma_f16_burst8(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                uint32_t b_hi, uint32_t idesc, uint32_t acc_first,
+                                                uint64_t* bar_tile0, uint64_t* bar_tile1, uint32_t leader) {
+#define HM_MMA_STEP(AOFF, BOFF)                                                   \
+    "add.u32 ta, %1, " #AOFF ";\n\t add.u32 tb, %3, " #BOFF ";\n\t"              \
+    "mov.b64 da, {ta, %2};\n\t mov.b64 db, {tb, %4};\n\t"                         \
+    "@l tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, q;\n\t"
+    // every issuing instruction is predicated on `leader` (the elected lane) instead of sitting in a divergent branch:
+    // the warp stays converged, no BSSY / BRA.DIV / BSYNC around each burst
+    asm volatile(
+        "{\n\t.reg .pred p, q, l;\n\t.reg .b64 da, db;\n\t.reg .b32 ta, tb;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t setp.eq.b32 q, %5, %5;\n\t setp.ne.b32 l, %23, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\t mov.b64 db, {%3, %4};\n\t"
+        "@l tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t"
+        HM_MMA_STEP(%9, %10) HM_MMA_STEP(%11, %12) HM_MMA_STEP(%13, %14)
+        "@l tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%7];\n\t"
+        HM_MMA_STEP(%15, %16) HM_MMA_STEP(%17, %18) HM_MMA_STEP(%19, %20) HM_MMA_STEP(%21, %22)
+        "@l tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%8];\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(acc_first),
+          "r"(smem_u32(bar_tile0)), "r"(smem_u32(bar_tile1)),
+          "n"(2), "n"(BK), "n"(4), "n"(2 * BK), "n"(6), "n"(3 * BK),
+          "n"(1024), "n"(BJ), "n"(1026), "n"(BJ + BK), "n"(1028), "n"(BJ + 2 * BK), "n"(1030), "n"(BJ + 3 * BK),
+          "r"(leader)
+        : "memory");
+#undef HM_MMA_STEP
+}
 // Arrive on an mbarrier when all previously issued tcgen05.mma of this thread completed.
 // (implies tcgen05.fence::before_thread_sync)
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile(
         "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
             smem_u32(bar))
+        : "memory");
+}
+// the same, issued only where `pred` != 0 (no divergent branch)
+__device__ __forceinline__ void umma_commit_if(uint64_t* bar, uint32_t pred) {
+    asm volatile(
+        "{\n\t.reg .pred l;\n\t setp.ne.b32 l, %1, 0;\n\t"
+        "@l tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)),
+        "r"(pred)
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() {
@@ -200,6 +255,22 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)
           "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr)
         : "memory");
+}
+
+// registers -> TMEM, same 32x32b shape: thread t of the warp writes row (lane base + t), columns [col, col+32)
+__device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+        "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+        "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
 // ---- UMMA descriptors -------------------------------------------------------------------

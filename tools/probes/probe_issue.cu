@@ -42,10 +42,10 @@ __device__ __forceinline__ uint32_t tile_deferred(uint32_t tmem, uint32_t a_lo, 
 }
 
 template <int GROUP, int NB, int MODE, int NDIM, bool ELECT>
-__global__ void __launch_bounds__(352, 1) mmaonly(int n_groups, long long* cycles_out, int spin) {
+__global__ void __launch_bounds__(608, 1) mmaonly(int n_groups, long long* cycles_out, int spin, int fill, int nacc, int per_tile_commit, int cols, int bcycle) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* bop = smem;
-    uint8_t* ringp = smem + 16384;
+    uint8_t* ringp = smem + 6 * 16384;
     uint64_t* bars = reinterpret_cast<uint64_t*>(ringp + NB * GROUP * 16384);
     uint32_t* slot = reinterpret_cast<uint32_t*>(bars + 32);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -53,8 +53,19 @@ __global__ void __launch_bounds__(352, 1) mmaonly(int n_groups, long long* cycle
         for (int i = 0; i < 32; ++i) mbar_init(&bars[i], 1);
         fence_barrier_init();
     }
-    if (warp == 1) { tmem_alloc(slot, 128); tmem_relinquish(); }
-    for (int i = threadIdx.x; i < 4096 * (1 + NB * GROUP); i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+    if (warp == 1) { tmem_alloc(slot, cols); tmem_relinquish(); }
+    // fill 0: all-zero operands; fill 1: pseudo-random fp16 values in [-2, 2) (sign, exponent 0x3c..0x3f, random
+    // mantissa) — does the tensor pipe's cycle count depend on the operand VALUES?
+    for (int i = threadIdx.x; i < 4096 * (6 + NB * GROUP); i += blockDim.x) {
+        uint32_t v = 0;
+        if (fill) {
+            uint32_t h = (i + 1) * 2654435761u + blockIdx.x * 40503u;
+            h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+            const uint32_t lo = (h & 0x83ffu) | 0x3c00u, hi = ((h >> 16) & 0x83ffu) | 0x3800u;
+            v = lo | (hi << 16);
+        }
+        reinterpret_cast<uint32_t*>(smem)[i] = v;
+    }
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -98,11 +109,14 @@ __global__ void __launch_bounds__(352, 1) mmaonly(int n_groups, long long* cycle
                 for (int b = 0; b < NB; ++b) {
                     if (MODE >= 2) mbar_wait(&bars[b], par);
                     if (leader) {
+                        const uint32_t acc = tmem + (nacc > 1 ? (b % nacc) * 128 : 0);   // accumulator block of this group
 #pragma unroll
-                        for (int j = 0; j < GROUP; ++j)
+                        for (int j = 0; j < GROUP; ++j) {
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
-                                umma_f16_lh(tmem, a_lo + (b * GROUP + j) * 1024 + 2 * k, a_hi, b_lo[k], b_hi, idesc, 1u);
+                                umma_f16_lh(acc, a_lo + (b * GROUP + j) * 1024 + 2 * k, a_hi, b_lo[k] + (bcycle ? (b * GROUP + j) * 1024 : 0), b_hi, idesc, 1u);
+                            if (per_tile_commit) umma_commit(&bars[16 + b * GROUP + j]);
+                        }
                         if (MODE >= 1) umma_commit(&bars[b]);
                     }
                     if (ELECT) __syncwarp();
@@ -148,30 +162,32 @@ __global__ void __launch_bounds__(352, 1) mmaonly(int n_groups, long long* cycle
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, 128); }
+    if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem, cols); }
 }
 
 template <int GROUP, int NB, int MODE, int NDIM = 128, bool ELECT = true>
-static void run_only(long long* dc, int spin = 0, int threads = 128) {
+static void run_only(long long* dc, int spin = 0, int threads = 128, int fill = 0, int grid = 1, int nacc = 1, int ptc = 0, int cols = 512, int bcycle = 0) {
     auto kern = mmaonly<GROUP, NB, MODE, NDIM, ELECT>;
-    const int smem = (NB * GROUP + 1) * 16384 + 1024;
+    const int smem = (NB * GROUP + 6) * 16384 + 1024;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     const int n_groups = (2400 / (GROUP * NB)) * NB;
     for (int rep = 0; rep < 2; ++rep) {
-        kern<<<1, threads, smem>>>(n_groups, dc, spin);
+        kern<<<grid, threads, smem>>>(n_groups, dc, spin, fill, nacc, ptc, cols, bcycle);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("err %s\n", cudaGetErrorString(e)); exit(1); }
     }
     long long c;
     cudaMemcpy(&c, dc, 8, cudaMemcpyDeviceToHost);
-    printf("spin=%d threads=%d %s N=%3d group=%d nb=%2d mode=%d  cycles per 4-MMA tile %8.1f  (tensor floor %d; per group %8.1f)\n", spin, threads, ELECT ? "elect " : "lane0 ", NDIM, GROUP, NB, MODE,
+    printf("cols=%d bcycle=%d nacc=%d ptc=%d fill=%d grid=%3d spin=%d threads=%d %s N=%3d group=%d nb=%2d mode=%d  cycles per 4-MMA tile %8.1f  (tensor floor %d; per group %8.1f)\n", cols, bcycle, nacc, ptc, fill, grid, spin, threads, ELECT ? "elect " : "lane0 ", NDIM, GROUP, NB, MODE,
            (double)c / (n_groups * GROUP), NDIM * 2, (double)c / n_groups);
 }
 
 int main() {
     long long* dc;
     cudaMalloc(&dc, 1024 * 8);
-    run_only<2, 3, 2>(dc, 0, 128);
-    for (int sp = 3; sp <= 7; ++sp) run_only<2, 3, 2>(dc, sp, 352);
+    run_only<2, 3, 2>(dc, 0, 128, 1, 148, 1, 0, 512, 0);
+    run_only<2, 3, 4>(dc, 0, 128, 1, 148, 1, 0, 512, 0);   // software-pipelined waits, descriptor arithmetic inside the asm block
+    run_only<1, 6, 4>(dc, 0, 128, 1, 148, 1, 0, 512, 0);   // the same with a barrier per 16 KB tile
+    run_only<2, 3, 4>(dc, 1, 608, 1, 148, 1, 0, 512, 0);
     return 0;
 }

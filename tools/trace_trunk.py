@@ -49,7 +49,9 @@ def main():
                   ", ".join(f"w{w}(SP{w % 4}) {c}" for w, c in sorted(warp_math.items())))
         summarize("producer", tr[0], {}, [(1, 2, "W1 group -> next W2 group issue"), (2, 1, "W2 group -> next W1 group"), (2, 2, "W2 -> W2")])
         summarize("mma", tr[1], MMA, [(1, 2, "wait D1_EMPTY"), (2, 3, "pw1 issue (6 tiles, waits ring)"), (4, 5, "wait Z_FULL"), (5, 6, "pw2 issue (6 tiles)"),
-                                      (3, 4, "pw1 end -> pw2 begin"), (6, 1, "pw2 end -> pw1 begin")])
+                                      (3, 4, "pw1 end -> pw2 begin"), (6, 1, "pw2 end -> pw1 begin"),
+                                      (10, 11, "pw1 burst 0"), (11, 12, "pw1 burst 1"), (12, 3, "pw1 burst 2"),
+                                      (20, 21, "pw2 burst 0"), (21, 22, "pw2 burst 1"), (22, 6, "pw2 burst 2")])
         summarize("compute", tr[2], CMP, [(1, 2, "wait D1_FULL"), (2, 3, "TMEM drain + bias/relu"), (3, 4, "depthwise math"), (4, 5, "wait Z_EMPTY"),
                                           (5, 6, "Z store + fence + publish"), (1, 6, "whole chunk"), (7, 8, "epi wait D2_FULL"), (8, 9, "epi part")])
         # TMA latency: producer's issue of a pair (tags 10+b / 20+b) -> issuer sees it full (same tag)
