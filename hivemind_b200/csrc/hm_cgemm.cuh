@@ -142,12 +142,18 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
             }
         }
     } else if (warp == 1) {
+        // Issue discipline as in hm_trunk.cuh: the tensor pipe queues only two or three MMAs, so the work between two
+        // bursts must be short — 8 MMAs + commit as one asm block (umma_f16_burst8), the NEXT weight stage's barrier
+        // probed (test_wait) before the burst and consumed after it.
         const bool leader = elect_one();
+        const uint32_t ld = leader ? 1u : 0u;
         constexpr uint32_t idesc = umma_idesc_16_bmn(128, 128, UMMA_FMT_16);
         const uint64_t a0 = umma_desc_sw128(smem_u32(smem));
         const uint64_t b0 = umma_desc_mn_sw128(smem_u32(smem_x), 8192, 1024);
+        const uint32_t a_lo = static_cast<uint32_t>(a0), b_lo = static_cast<uint32_t>(b0);
         int ws = 0, xs = 0;
         uint32_t wphase = 0, xphase = 0;
+        uint32_t have_w = 0;   // full_w[ws] already known complete
         for (int ky = 0; ky < p.ksize; ++ky) {
             for (int kp = 0; kp < kpairs; ++kp) {
                 mbar_wait(&full_x[xs], xphase);
@@ -155,11 +161,16 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
                 const int nk = kp + 1 < kpairs ? 8 : p.ksteps_last;   // K steps that hold real channels
                 for (int kx = 0; kx < p.ksize; ++kx) {       // accumulator = horizontal offset kx
                     const uint32_t d = tmem_base + kx * 128;
-                    mbar_wait(&full_w[ws], wphase);
+                    if (!have_w) mbar_wait(&full_w[ws], wphase);
                     tc_fence_after();
-                    if (leader) {
-                        const uint32_t wo = ws * (CG_STAGE_BYTES / 16);
-                        const uint32_t acc0 = (ky | kp) ? 1u : 0u;  // first tile of this accumulator
+                    const int nws = ws + 1 == n_w ? 0 : ws + 1;
+                    const uint32_t nphase = ws + 1 == n_w ? wphase ^ 1 : wphase;
+                    const uint32_t next_ok = mbar_test_wait(&full_w[nws], nphase);
+                    const uint32_t wo = ws * (CG_STAGE_BYTES / 16);
+                    const uint32_t acc0 = (ky | kp) ? 1u : 0u;  // first tile of this accumulator
+                    if (nk == 8) {
+                        if (leader) umma_f16_burst8<1024, 2, 1024, 128, idesc, false>(d, a_lo + wo, b_lo + xo, acc0, &empty_w[ws], &empty_w[ws], ld);
+                    } else if (leader) {
 #pragma unroll
                         for (int j = 0; j < 2; ++j) {
 #pragma unroll
@@ -169,10 +180,12 @@ cgemm_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW,
                                              (j | k) ? 1u : acc0);
                         }
                         umma_commit(&empty_w[ws]);
-                        if (kx == p.ksize - 1) umma_commit(&empty_x[xs]);
                     }
+                    if (kx == p.ksize - 1) umma_commit_if(&empty_x[xs], ld);
                     __syncwarp();
-                    if (++ws == n_w) { ws = 0; wphase ^= 1; }
+                    have_w = next_ok;
+                    ws = nws;
+                    wphase = nphase;
                 }
                 if (++xs == n_x) { xs = 0; xphase ^= 1; }
             }

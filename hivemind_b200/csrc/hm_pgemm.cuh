@@ -104,14 +104,17 @@ pgemm_kernel(const PgemmParams p, const __grid_constant__ CUtensorMap tmW, const
             }
         }
     } else if (warp == 1) {
+        // issue discipline as in hm_trunk.cuh / hm_cgemm.cuh: fused 8-MMA bursts, next weight barrier probed early
         const bool leader = elect_one();
+        const uint32_t ld = leader ? 1u : 0u;
         // A = activations MN-major (bit 15), B = weights K-major
         const uint32_t idesc = umma_idesc_16(128, static_cast<uint32_t>(p.npad), UMMA_FMT_16) | (1u << 15);
         const uint64_t w0 = umma_desc_sw128(smem_u32(smem));
         const uint64_t x0 = umma_desc_mn_sw128(smem_u32(smem_x), 8192, 1024);
+        const uint32_t w_lo = static_cast<uint32_t>(w0), x_lo = static_cast<uint32_t>(x0);
         const uint32_t wunits = static_cast<uint32_t>(wbytes) >> 4;   // stage size in 16-byte descriptor units
         int ws = 0, xs = 0;
-        uint32_t wphase = 0, xphase = 0;
+        uint32_t wphase = 0, xphase = 0, have_w = 0;
         for (int ky = 0; ky < 3; ++ky) {
             for (int kp = 0; kp < kpairs; ++kp) {
                 mbar_wait(&full_x[xs], xphase);
@@ -119,11 +122,18 @@ pgemm_kernel(const PgemmParams p, const __grid_constant__ CUtensorMap tmW, const
                 const int nk = kp + 1 < kpairs ? 8 : p.ksteps_last;
                 for (int kx = 0; kx < 3; ++kx) {
                     const uint32_t d = tmem_base + kx * p.npad;
-                    mbar_wait(&full_w[ws], wphase);
+                    if (!have_w) mbar_wait(&full_w[ws], wphase);
                     tc_fence_after();
-                    if (leader) {
-                        const uint32_t wo = ws * wunits;
-                        const uint32_t acc0 = (ky | kp) ? 1u : 0u;
+                    const int nws = ws + 1 == PG_WSTAGES ? 0 : ws + 1;
+                    const uint32_t nphase = ws + 1 == PG_WSTAGES ? wphase ^ 1 : wphase;
+                    const uint32_t next_ok = mbar_test_wait(&full_w[nws], nphase);
+                    const uint32_t wo = ws * wunits;
+                    const uint32_t acc0 = (ky | kp) ? 1u : 0u;
+                    if (nk == 8 && p.npad == 160) {        // second K block of a stage: 160 rows x 128 B = 1280 units on
+                        if (leader) umma_f16_burst8<1024, 128, 1280, 2, umma_idesc_16(128, 160, UMMA_FMT_16) | (1u << 15), false>(d, x_lo + xo, w_lo + wo, acc0, &empty_w[ws], &empty_w[ws], ld);
+                    } else if (nk == 8 && p.npad == 80) {
+                        if (leader) umma_f16_burst8<1024, 128, 640, 2, umma_idesc_16(128, 80, UMMA_FMT_16) | (1u << 15), false>(d, x_lo + xo, w_lo + wo, acc0, &empty_w[ws], &empty_w[ws], ld);
+                    } else if (leader) {
 #pragma unroll
                         for (int j = 0; j < 2; ++j) {
 #pragma unroll
@@ -133,10 +143,12 @@ pgemm_kernel(const PgemmParams p, const __grid_constant__ CUtensorMap tmW, const
                                              (j | k) ? 1u : acc0);
                         }
                         umma_commit(&empty_w[ws]);
-                        if (kx == 2) umma_commit(&empty_x[xs]);
                     }
+                    if (kx == 2) umma_commit_if(&empty_x[xs], ld);
                     __syncwarp();
-                    if (++ws == PG_WSTAGES) { ws = 0; wphase ^= 1; }
+                    have_w = next_ok;
+                    ws = nws;
+                    wphase = nphase;
                 }
                 if (++xs == PG_XSTAGES) { xs = 0; xphase ^= 1; }
             }

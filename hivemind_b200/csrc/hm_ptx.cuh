@@ -173,32 +173,37 @@ __device__ __forceinline__ void umma_f16_lh(uint32_t d_tmem, uint32_t a_lo, uint
 // behind the running one (tools/probes/probe_issue.cu: a few extra instructions per burst already cost 8-10 % once
 // they are hoisted in front of it), so everything the issuing thread does between two bursts — barrier wait,
 // ~40 R2UR/UMOV of descriptor set-up — has to fit into ~150 cycles or the pipe starves; inside the block each MMA's
-// set-up runs while the queue is still full.  Descriptor low words: A tile j, step k = a_lo + j*1024 + 2k (16-byte
-// units); B = b_lo + j*BJ + k*BK.  acc_first: accumulate flag of the very first MMA (the others accumulate).
-template <int BJ, int BK>
-__device__ __forceinline__ void umma_f16_burst8(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
-                                                uint32_t b_hi, uint32_t idesc, uint32_t acc_first,
+// set-up runs while the queue is still full.  Descriptor low words (16-byte units): first operand of tile j, step k =
+// a_lo + j*AJ + k*AK; second = b_lo + j*BJ + k*BK.  acc_first: accumulate flag of the very first MMA (the others accumulate).
+// MID_COMMIT = false: no commit after the first tile (callers with one barrier per 32 KB stage).  The descriptor HIGH
+// words and the instruction descriptor are compile-time immediates (HI_A / HI_B / IDESC): they cost a UMOV, not a
+// vector register + R2UR each.
+constexpr uint32_t UMMA_DESC_HI_SW128 = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024 B, version 1, SWIZZLE_128B
+template <int AJ, int AK, int BJ, int BK, uint32_t IDESC, bool MID_COMMIT = true>
+__device__ __forceinline__ void umma_f16_burst8(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t acc_first,
                                                 uint64_t* bar_tile0, uint64_t* bar_tile1, uint32_t leader) {
 #define HM_MMA_STEP(AOFF, BOFF)                                                   \
-    "add.u32 ta, %1, " #AOFF ";\n\t add.u32 tb, %3, " #BOFF ";\n\t"              \
-    "mov.b64 da, {ta, %2};\n\t mov.b64 db, {tb, %4};\n\t"                         \
-    "@l tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, q;\n\t"
-    // every issuing instruction is predicated on `leader` (the elected lane) instead of sitting in a divergent branch:
-    // the warp stays converged, no BSSY / BRA.DIV / BSYNC around each burst
+    "add.u32 ta, %1, " #AOFF ";\n\t add.u32 tb, %2, " #BOFF ";\n\t"              \
+    "mov.b64 da, {ta, %22};\n\t mov.b64 db, {tb, %22};\n\t"                       \
+    "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %23, q;\n\t"
+    // called by the elected lane only, inside a warp-uniform `if (leader)`: predicating every instruction on a per-lane
+    // predicate instead makes ptxas carry the descriptors in vector registers (two R2UR per descriptor)
+    (void)leader;
     asm volatile(
-        "{\n\t.reg .pred p, q, l;\n\t.reg .b64 da, db;\n\t.reg .b32 ta, tb;\n\t"
-        "setp.ne.b32 p, %6, 0;\n\t setp.eq.b32 q, %5, %5;\n\t setp.ne.b32 l, %23, 0;\n\t"
-        "mov.b64 da, {%1, %2};\n\t mov.b64 db, {%3, %4};\n\t"
-        "@l tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t"
-        HM_MMA_STEP(%9, %10) HM_MMA_STEP(%11, %12) HM_MMA_STEP(%13, %14)
-        "@l tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%7];\n\t"
-        HM_MMA_STEP(%15, %16) HM_MMA_STEP(%17, %18) HM_MMA_STEP(%19, %20) HM_MMA_STEP(%21, %22)
-        "@l tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%8];\n\t}"
-        ::"r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(acc_first),
-          "r"(smem_u32(bar_tile0)), "r"(smem_u32(bar_tile1)),
-          "n"(2), "n"(BK), "n"(4), "n"(2 * BK), "n"(6), "n"(3 * BK),
-          "n"(1024), "n"(BJ), "n"(1026), "n"(BJ + BK), "n"(1028), "n"(BJ + 2 * BK), "n"(1030), "n"(BJ + 3 * BK),
-          "r"(leader)
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t.reg .b32 ta, tb;\n\t"
+        "setp.ne.b32 p, %3, 0;\n\t setp.eq.b32 q, %0, %0;\n\t"
+        "mov.b64 da, {%1, %22};\n\t mov.b64 db, {%2, %22};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %23, p;\n\t"
+        HM_MMA_STEP(%8, %9) HM_MMA_STEP(%10, %11) HM_MMA_STEP(%12, %13)
+        "setp.ne.b32 p, %7, 0;\n\t"
+        "@p tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%4];\n\t"
+        HM_MMA_STEP(%14, %15) HM_MMA_STEP(%16, %17) HM_MMA_STEP(%18, %19) HM_MMA_STEP(%20, %21)
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%5];\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(acc_first),
+          "r"(smem_u32(bar_tile0)), "r"(smem_u32(bar_tile1)), "r"(leader), "r"(MID_COMMIT ? 1u : 0u),
+          "n"(AK), "n"(BK), "n"(2 * AK), "n"(2 * BK), "n"(3 * AK), "n"(3 * BK),
+          "n"(AJ), "n"(BJ), "n"(AJ + AK), "n"(BJ + BK), "n"(AJ + 2 * AK), "n"(BJ + 2 * BK), "n"(AJ + 3 * AK), "n"(BJ + 3 * BK),
+          "n"(UMMA_DESC_HI_SW128), "n"(IDESC)
         : "memory");
 #undef HM_MMA_STEP
 }

@@ -364,11 +364,10 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         const uint64_t a0d = umma_desc_sw128(smem_u32(smem + TR_RING_OFF));
         const uint64_t xd0d = umma_desc_mn_sw128(smem_u32(smem + TR_X_OFF), 8192, 1024);
         const uint64_t zd0d = umma_desc_mn_sw128(smem_u32(smem + TR_Z_OFF), 8192, 1024);
-        const uint32_t a0 = static_cast<uint32_t>(a0d), a_hi = static_cast<uint32_t>(a0d >> 32);
+        const uint32_t a0 = static_cast<uint32_t>(a0d);   // the high words of all four are UMMA_DESC_HI_SW128
         const uint32_t xd0 = static_cast<uint32_t>(xd0d), zd0 = static_cast<uint32_t>(zd0d);
-        const uint32_t b_hi = static_cast<uint32_t>(xd0d >> 32);
         const uint64_t zmd = umma_desc_sw128(smem_u32(smem + TR_Z_OFF));   // ECA means: K-major, 16 rows per K block
-        const uint32_t zm0 = static_cast<uint32_t>(zmd), zm_hi = static_cast<uint32_t>(zmd >> 32);
+        const uint32_t zm0 = static_cast<uint32_t>(zmd);
         // `have` = the full-barrier of ring pair 0 of the current lap is already known complete
         uint32_t have = 0;
         // one lap over the ring = three bursts; kind 0 = pw1 (D1 = W1 . X), 1 = pw2 (D2[m] += W2 . Z), 2 = ECA (G[m] = Wc . means)
@@ -384,20 +383,21 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 const int nb = b2 + 1 == TR_PAIRS ? 0 : b2 + 1;
                 const uint32_t npar = b2 + 1 == TR_PAIRS ? par ^ 1 : par;
                 const uint32_t next_ok = mbar_test_wait(&bars[TB_PAIR_FULL + nb], npar);
-                const uint32_t ld = leader ? 1u : 0u;
-                if (KIND == 0) {
-                    umma_f16_burst8<1024, 128>(tm_d1, a0 + (2 * b2) * 1024, a_hi, xd0 + (2 * b2) * 1024, b_hi, idesc,
+                const uint32_t ld = 1u;
+                if (!leader) {
+                } else if (KIND == 0) {
+                    umma_f16_burst8<1024, 2, 1024, 128, idesc>(tm_d1, a0 + (2 * b2) * 1024, xd0 + (2 * b2) * 1024,
                                                b2 ? 1u : 0u, &bars[TB_TILE_EMPTY + 2 * b2], &bars[TB_TILE_EMPTY + 2 * b2 + 1], ld);
                     if (b2 == TR_PAIRS - 1) umma_commit_if(&bars[TB_D1_FULL], ld);
                 } else if (KIND == 1) {   // always accumulates: D2 is the running fp32 residual stream
-                    umma_f16_burst8<1024, 128>(tm_d2 + b2 * 128, a0 + (2 * b2) * 1024, a_hi, zd0, b_hi, idesc, 1u,
+                    umma_f16_burst8<1024, 2, 1024, 128, idesc>(tm_d2 + b2 * 128, a0 + (2 * b2) * 1024, zd0, 1u,
                                                &bars[TB_TILE_EMPTY + 2 * b2], &bars[TB_TILE_EMPTY + 2 * b2 + 1], ld);
                     if (last_chunk) umma_commit_if(&bars[TB_D2_FULL + b2], ld);  // output block m = b2 complete
                     if (b2 == TR_PAIRS - 1) umma_commit_if(&bars[TB_Z_EMPTY], ld);
                 } else {
                     constexpr uint32_t idesc_eca = umma_idesc_16(128, 16, UMMA_FMT_16);
-                    umma_f16_burst8<128, 2>(tm_d1 + m_eca * 16, a0 + (2 * b2) * 1024, a_hi, zm0 + (2 * b2) * 128, zm_hi,
-                                            idesc_eca, b2 ? 1u : 0u, &bars[TB_TILE_EMPTY + 2 * b2], &bars[TB_TILE_EMPTY + 2 * b2 + 1], ld);
+                    umma_f16_burst8<1024, 2, 128, 2, idesc_eca>(tm_d1 + m_eca * 16, a0 + (2 * b2) * 1024, zm0 + (2 * b2) * 128,
+                                            b2 ? 1u : 0u, &bars[TB_TILE_EMPTY + 2 * b2], &bars[TB_TILE_EMPTY + 2 * b2 + 1], ld);
                     if (m_eca == 2 && b2 == TR_PAIRS - 1) umma_commit_if(&bars[TB_ECA_DONE], ld);
                 }
                 __syncwarp();

@@ -81,6 +81,17 @@ inline uint64_t mix_seed(uint64_t seed, uint64_t value) {
 
 struct Stats {
     std::atomic<uint64_t> nodes{0}, evals{0}, terminals{0}, requests{0}, collisions{0}, moves{0}, games{0}, samples{0};
+    // host-time attribution (TSC ticks summed over threads; --profile 1): select_and_expand | terminal classification |
+    // pack + move generation (LeafBatch::add) | expand_leaf_node | backup | waiting for the device | playing moves
+    std::atomic<uint64_t> tSelect{0}, tTerminal{0}, tPack{0}, tExpand{0}, tBackup{0}, tWait{0}, tMove{0};
+    bool profile = false;
+};
+inline uint64_t ticks() { return __builtin_ia32_rdtsc(); }
+struct Lap {   // adds the ticks since construction / the last lap to a counter when profiling is on
+    explicit Lap(const Stats& s) : on(s.profile), t(on ? ticks() : 0) {}
+    void to(std::atomic<uint64_t>& c) { if (on) { const uint64_t n = ticks(); c.fetch_add(n - t, std::memory_order_relaxed); t = n; } }
+    bool on;
+    uint64_t t;
 };
 
 // One leaf on its way through the evaluator (the role of LeafContext, searchthread.h:52-78).
@@ -114,7 +125,9 @@ public:
             ++attempts;
             std::vector<TrajectoryEntry>& path = m_tree.trajectoryBuffer;
             path.clear();
+            Lap lap(stats);
             LeafSelection sel = m_tree.select_and_expand(*m_board, m_timeAdvantage);
+            lap.to(stats.tSelect);
             auto rewind = [&] {
                 for (auto it = path.rbegin(); it != path.rend(); ++it)
                     if (it->action.moveA != Stockfish::MOVE_NONE || it->action.moveB != Stockfish::MOVE_NONE)
@@ -167,6 +180,7 @@ public:
                     }
                 }
             }
+            lap.to(stats.tTerminal);
             if (!leaf.terminal) {
                 if (!leaf.reserved) {   // someone else (an in-flight request) owns the evaluation
                     stats.collisions.fetch_add(1, std::memory_order_relaxed);
@@ -180,6 +194,7 @@ public:
                 leaf.bOnTurn = m_board->side_to_move(BOARD_B) == ~leaf.team;
                 // THE fused hand-over: packed record + legal-move lists (+ capture flags), generated once, here
                 leaf.slot = batch.add(*m_board, leaf.team, sitPlaneActive);
+                lap.to(stats.tPack);
             }
             rewind();
             leaf.trajectory = std::move(path);   // select_and_expand's buffer is cleared before its next use
@@ -213,10 +228,13 @@ public:
                 m_priors[bn].assign(pr, pr + n);
                 m_captures[bn].assign(cp, cp + n);
             }
+            Lap lap(stats);
             m_tree.expand_leaf_node(leaf.node.get(), m_actions[0], m_actions[1], m_priors[0], m_priors[1], leaf.timeAdvantage,
                                     leaf.aOnTurn, leaf.bOnTurn, m_captures[0], m_captures[1], leaf.hash);
             leaf.node->release_evaluation_reservation();
+            lap.to(stats.tExpand);
             m_tree.backup(path, *m_board, batch.value(leaf.slot));   // already shaped (searchthread.cc:569-619) on the device
+            lap.to(stats.tBackup);
             stats.evals.fetch_add(1, std::memory_order_relaxed);
         }
         m_info->increment_nodes(1);
@@ -454,11 +472,16 @@ private:
 
     void finish(int h, bool playMoves) {
         hm::LeafBatch& batch = m_batches[h];
-        if (!batch.collect(m_engine, slot(h))) throw std::runtime_error(std::string("collect failed: ") + hm_last_error());
+        Lap lap(m_stats);
+        const bool got = batch.collect(m_engine, slot(h));
+        lap.to(m_stats.tWait);
+        if (!got) throw std::runtime_error(std::string("collect failed: ") + hm_last_error());
         for (Leaf& leaf : m_leaves[h]) m_games[leaf.game]->absorb(leaf, batch, m_stats);
         m_leaves[h].clear();
+        lap.t = lap.on ? ticks() : 0;
         if (playMoves)
             for (size_t g = static_cast<size_t>(h); g < m_games.size(); g += 2) m_games[g]->advance(m_stats, m_writer.get());
+        lap.to(m_stats.tMove);
     }
 
     const Config& m_cfg;
@@ -478,6 +501,7 @@ private:
 
 int main(int argc, char** argv) {
     fused::Config cfg;
+    bool profile = false;
     for (int i = 1; i + 1 < argc; i += 2) {
         const std::string k = argv[i], v = argv[i + 1];
         if (k == "--model") cfg.model = v;
@@ -492,6 +516,7 @@ int main(int argc, char** argv) {
         else if (k == "--seed") cfg.seed = std::stoull(v);
         else if (k == "--chunks") cfg.chunkDir = v;
         else if (k == "--chunk-samples") cfg.chunkSamples = std::stoull(v);
+        else if (k == "--profile") profile = v != "0";
         else { std::cerr << "unknown option " << k << std::endl; return 2; }
     }
     if (cfg.model.empty() || cfg.games == 0 || cfg.nodes == 0 || cfg.batch == 0) {
@@ -514,6 +539,7 @@ int main(int argc, char** argv) {
     if (!cfg.chunkDir.empty()) std::filesystem::create_directories(cfg.chunkDir);
 
     fused::Stats stats;
+    stats.profile = profile;
     std::vector<std::unique_ptr<fused::Worker>> workers;
     size_t first = 0;
     for (size_t t = 0; t < cfg.threads; ++t) {
@@ -546,6 +572,15 @@ int main(int argc, char** argv) {
               << ", \"avg_batch_fill\": " << (requests ? fill / static_cast<double>(requests) : 0.0)
               << ", \"collisions\": " << stats.collisions.load() << ", \"moves_played\": " << stats.moves.load()
               << ", \"games_finished\": " << stats.games.load() << ", \"samples_written\": " << stats.samples.load()
-              << ", \"failed\": " << (failed ? "true" : "false") << "}" << std::endl;
+              << ", \"failed\": " << (failed ? "true" : "false");
+    if (profile) {
+        const double all = static_cast<double>(stats.tSelect + stats.tTerminal + stats.tPack + stats.tExpand + stats.tBackup + stats.tWait + stats.tMove);
+        auto pct = [&](const std::atomic<uint64_t>& c) { return all > 0 ? 100.0 * static_cast<double>(c.load()) / all : 0.0; };
+        std::cout << ", \"host_time_pct\": {\"select_and_expand\": " << pct(stats.tSelect) << ", \"terminal_classification\": " << pct(stats.tTerminal)
+                  << ", \"pack_and_movegen\": " << pct(stats.tPack) << ", \"expand_leaf_node\": " << pct(stats.tExpand)
+                  << ", \"backup\": " << pct(stats.tBackup) << ", \"wait_for_device\": " << pct(stats.tWait)
+                  << ", \"play_moves\": " << pct(stats.tMove) << "}";
+    }
+    std::cout << "}" << std::endl;
     return failed ? 1 : 0;
 }
