@@ -27,7 +27,8 @@
 //                Z  [2][2 pos][64 ch][64 sq]                                     = B operand of pw2
 //                ring of 6 x 16 KB weight tiles [128 rows x 64 K] K-major        = A operands
 // TMEM (512 columns): D2 = 3 x 128 columns (fp32 residual stream + pw2 accumulation), D1 = 128.
-// Warps (576 threads): 0 = TMA producer, 1 = MMA issuer, 2-17 = compute.  A compute thread is
+// Warps (640 threads): 0-15 = compute, 16 = TMA producer, 17 = MMA issuer, 18-19 idle (they complete the control
+// warpgroup that hands registers to the compute warpgroups with setmaxnreg).  A compute thread is
 // (TMEM lane quarter q = warp & 3 -> channel r = 32q + lane, position h, board half t): sixteen
 // compute warps = four per sub-partition, so the depthwise FFMA2 chains, the TMEM loads and the
 // conversions of different warps overlap instead of running phase-locked (two warps per
@@ -82,7 +83,8 @@ constexpr int TR_TRACE_CAP = 2048;
 
 constexpr int TR_COMPUTE_WARPS = 16;
 constexpr int TR_COMPUTE = TR_COMPUTE_WARPS * 32;
-constexpr int TR_THREADS = 64 + TR_COMPUTE;
+constexpr int TR_PRODUCER_WARP = TR_COMPUTE_WARPS, TR_MMA_WARP = TR_COMPUTE_WARPS + 1;
+constexpr int TR_THREADS = TR_COMPUTE + 128;   // + one warpgroup: producer, MMA issuer, two idle warps
 // Weight ring: 6 slots of 16 KB = exactly one "group" (the 6 W1 tiles of a chunk's pw1, or the 6
 // W2 tiles of its pw2), so slot indices are compile-time inside the fully unrolled group loops and
 // the barrier parity simply toggles per group.  One "full" barrier guards TWO slots (32 KB,
@@ -238,7 +240,6 @@ __device__ __forceinline__ void trunk_chunk(const float* __restrict__ par, int r
     TR_MARK(2, 6);
 }
 
-// 18 warps are allocated as 20 (warp-allocation granularity 4): 640 x 96 registers = 61,440 of the SM's 65,536
 __global__ void __launch_bounds__(TR_THREADS, 1)
 trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUtensorMap tmX,
              const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2) {
@@ -274,7 +275,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         }
         fence_barrier_init();
     }
-    if (warp == 1) {
+    if (warp == TR_MMA_WARP) {
         tmem_alloc(tmem_slot, 512);
         tmem_relinquish();
     }
@@ -289,7 +290,15 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
     // counters, descriptor arithmetic stay warp-uniform -> uniform registers, no per-lane
     // election loops around every UTMALDG / UTCHMMA); only the issuing instructions themselves
     // are predicated on one elected lane.
-    if (warp == 0) {
+    // Register budget: 640 threads x 96 at launch.  Every spill goes to L2 — with 224 KB of shared memory in use there
+    // is next to no L1 left — so local-memory traffic is kept out of the hot loops (no dynamically indexed register
+    // arrays: that alone was worth 5.6 % of the kernel).  Handing registers from the control warpgroup to the compute
+    // warpgroups (setmaxnreg 64 / 104) was tried: ptxas then spills the MMA issuer and gives the depthwise nothing.
+#ifdef HM_TRUNK_SETMAXNREG
+    if (warp >= TR_COMPUTE_WARPS) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;" ::: "memory");
+    else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;" ::: "memory");
+#endif
+    if (warp == TR_PRODUCER_WARP) {
         // ================================ TMA producer ================================
         const bool leader = elect_one();
         if (leader) {
@@ -348,7 +357,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 group_w2(g0 + c);
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == TR_MMA_WARP) {
         // ================================ MMA issuer ================================
         // Issue discipline (tools/probes/probe_issue.cu): the tensor pipe queues only two or three MMAs behind the one
         // it runs, so whatever this thread does BETWEEN two bursts of MMAs must fit into ~150 cycles.  Hence (1) a
@@ -448,9 +457,9 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                 TR_MARK(1, 6);
             }
         }
-    } else {
+    } else if (warp < TR_COMPUTE_WARPS) {
         // ================================ compute warps ================================
-        const int cw = warp - 2;
+        const int cw = warp;
         const int q = warp & 3;             // TMEM lane quarter this warp may access
         const int h = (cw >> 2) & 1;        // position of the tile handled by this thread
         const int t = cw >> 3;              // board half: 0 = ranks 0-3 (squares 0-31), 1 = ranks 4-7
@@ -493,7 +502,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
 
         uint32_t d1_n = 0, z_n = 0, eca_cnt = 0;
         int trace_n = 0;
-        unsigned long long* const ctrace = warp == 2 ? tr_trace : nullptr;
+        unsigned long long* const ctrace = warp == 0 ? tr_trace : nullptr;
         // this thread's D1 rows: local row l of its half = image row (t ? 7 - l : l) of position h
         const uint32_t tm_row0 = tm_d1 + lane_off + static_cast<uint32_t>(h * 64 + t * 56);
         const int row_step = t ? -8 : 8;
@@ -521,14 +530,15 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                     uint32_t gv[8];
                     tmem_ld_32x32b_x8(tm_d1 + lane_off + m * 16, gv);
                     tmem_ld_wait();
-                    const float acc = (__uint_as_float(gv[h]) + __uint_as_float(gv[2 + h])) +
-                                      (__uint_as_float(gv[4 + h]) + __uint_as_float(gv[6 + h]));
+                    // columns h, 2+h, 4+h, 6+h (selected without indexing the register array dynamically)
+                    const float acc = (__uint_as_float(h ? gv[1] : gv[0]) + __uint_as_float(h ? gv[3] : gv[2])) +
+                                      (__uint_as_float(h ? gv[5] : gv[4]) + __uint_as_float(h ? gv[7] : gv[6]));
                     // torch.nn.Hardsigmoid: relu6(x + 3) / 6
                     gate[m] = fminf(fmaxf((acc + ebias[m]) * (1.0f / 6.0f) + 0.5f, 0.0f), 1.0f);
                 }
                 // every thread has read ALL its gates before any X_READY below can complete (it needs all 16
                 // warps), so the first pw1 of this block may overwrite D1 as soon as X_READY[0] fires
-#pragma unroll 1
+#pragma unroll
                 for (int m = 0; m < 3; ++m) {
                     uint32_t a[32];
                     const uint32_t taddr = tm_d2 + lane_off + m * 128 + col_half;
@@ -629,7 +639,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
                     *reinterpret_cast<act_t*>(base + n_hi * 128 + (((k >> 3) ^ n_hi) << 4)) = hi;
                     *reinterpret_cast<act_t*>(base + n_lo * 128 + (((k >> 3) ^ n_lo) << 4)) = lo;
                 }
-                for (int i = threadIdx.x - 64; i < 6 * 8 * 8; i += TR_COMPUTE) {
+                for (int i = threadIdx.x; i < 6 * 8 * 8; i += TR_COMPUTE) {
                     const int kb = i >> 6, rem = i & 63;
                     *reinterpret_cast<uint4*>(zm + kb * 2048 + (8 + (rem >> 3)) * 128 + ((rem & 7) << 4)) = make_uint4(0, 0, 0, 0);
                 }
@@ -640,7 +650,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
         }
         // ---- run output: shared-memory tile -> global (TMA store) ----
         named_bar_sync(1, TR_COMPUTE);
-        if (threadIdx.x == 64) {
+        if (threadIdx.x == 0) {
             for (int kb = 0; kb < 6; ++kb) tma_store_3d(&tmX, smem + TR_X_OFF + kb * 16384, 0, kb * 64, tile * 2);
             bulk_commit_group();
             bulk_wait_group0();
@@ -648,7 +658,7 @@ trunk_kernel(const __grid_constant__ TrunkParams p, const __grid_constant__ CUte
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) {
+    if (warp == TR_MMA_WARP) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
     }
