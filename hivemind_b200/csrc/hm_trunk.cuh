@@ -130,42 +130,38 @@ __device__ __forceinline__ void tr_wait_empty(uint64_t* bar, uint32_t k) { mbar_
 // E[j] = (o[2j], o[2j+1]), taps with an odd offset into the odd-aligned pairs O[k] = (o[2k-1], o[2k]);
 // one scalar add per square joins them.
 template <int KS>
-__device__ __forceinline__ void dw_half(const float (&y)[(4 + KS / 2) * 8], const float (&w)[KS * KS], float bd,
-                                        uint32_t (&packed)[16]) {
+__device__ __forceinline__ void dw_row(int lo, const float (&y)[(4 + KS / 2) * 8], const float (&w)[KS * KS], float bd,
+                                       uint32_t (&out)[4]) {
     constexpr int H = KS / 2;
+    float2 E[4], O[5];
 #pragma unroll
-    for (int lo = 0; lo < 4; ++lo) {
-        float2 E[4], O[5];
+    for (int j = 0; j < 4; ++j) E[j] = make_float2(bd, bd);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) E[j] = make_float2(bd, bd);
+    for (int j = 0; j < 5; ++j) O[j] = make_float2(0.0f, 0.0f);
 #pragma unroll
-        for (int j = 0; j < 5; ++j) O[j] = make_float2(0.0f, 0.0f);
+    for (int ky = 0; ky < KS; ++ky) {
+        const int li = lo + ky - H;
+        if (li < 0) continue;           // off the board (li <= 3 + H < NR always)
 #pragma unroll
-        for (int ky = 0; ky < KS; ++ky) {
-            const int li = lo + ky - H;
-            if (li < 0) continue;           // off the board (li <= 3 + H < NR always)
+        for (int kx = 0; kx < KS; ++kx) {
+            const int dx = kx - H;
+            const float2 ww = make_float2(w[ky * KS + kx], w[ky * KS + kx]);
 #pragma unroll
-            for (int kx = 0; kx < KS; ++kx) {
-                const int dx = kx - H;
-                const float2 ww = make_float2(w[ky * KS + kx], w[ky * KS + kx]);
-#pragma unroll
-                for (int a = 0; a < 4; ++a) {
-                    const float2 in = make_float2(y[li * 8 + 2 * a], y[li * 8 + 2 * a + 1]);
-                    if ((dx & 1) == 0) {
-                        const int j = a - dx / 2;          // o[x] += w * in[x + dx]
-                        if (j < 0 || j > 3) continue;
-                        E[j] = __ffma2_rn(in, ww, E[j]);
-                    } else {
-                        const int k = a + (1 - dx) / 2;    // pair (o[2a-dx], o[2a+1-dx]) = O[k]
-                        O[k] = __ffma2_rn(in, ww, O[k]);
-                    }
+            for (int a = 0; a < 4; ++a) {
+                const float2 in = make_float2(y[li * 8 + 2 * a], y[li * 8 + 2 * a + 1]);
+                if ((dx & 1) == 0) {
+                    const int j = a - dx / 2;          // o[x] += w * in[x + dx]
+                    if (j < 0 || j > 3) continue;
+                    E[j] = __ffma2_rn(in, ww, E[j]);
+                } else {
+                    const int k = a + (1 - dx) / 2;    // pair (o[2a-dx], o[2a+1-dx]) = O[k]
+                    O[k] = __ffma2_rn(in, ww, O[k]);
                 }
             }
         }
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-            packed[lo * 4 + j] = pack_act2_relu(E[j].x + O[j].y, E[j].y + O[j + 1].x);
     }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) out[j] = pack_act2_relu(E[j].x + O[j].y, E[j].y + O[j + 1].x);
 }
 
 // One 128-channel chunk on a compute thread (channel r, position h, board half t):
@@ -217,22 +213,36 @@ __device__ __forceinline__ void trunk_chunk(const float* __restrict__ par, int r
             }
     }
     TR_MARK(2, 3);
-    uint32_t packed[16];
-    if (TR_DBG(1)) {
-#pragma unroll
-        for (int j = 0; j < 16; ++j) packed[j] = __float_as_uint(y[2 * j] + w[j % (KS * KS)] + bd);
-    } else {
-        dw_half<KS>(y, w, bd, packed);
-    }
-    TR_MARK(2, 4);
-    tr_wait_empty(&bars[TB_Z_EMPTY], z_n);  // pw2 of the previous chunk has consumed Z
-    TR_MARK(2, 5);
-#pragma unroll
-    for (int lo = 0; lo < 4; ++lo) {
+    auto store_row = [&](int lo, const uint32_t (&o)[4]) {
         const int yo = t ? 7 - lo : lo;     // image row of local output row lo = 16-byte piece of the Z row
-        if (TR_DBG(4) && packed[4 * lo] != 0x12345678u) continue;
-        *reinterpret_cast<uint4*>(zrow + ((yo ^ key) << 4)) =
-            make_uint4(packed[4 * lo], packed[4 * lo + 1], packed[4 * lo + 2], packed[4 * lo + 3]);
+        if (TR_DBG(4) && o[0] != 0x12345678u) return;
+        *reinterpret_cast<uint4*>(zrow + ((yo ^ key) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+    };
+    if (KS == 5) {
+        // The 5x5 chunks are the compute-bound ones: by the time two of the four output rows are done, pw2 of the
+        // previous chunk has long released Z, so the rows are stored as they are finished and only two rows of packed
+        // results are ever live (the register pressure of holding all four spills — to L2, see the kernel comment).
+        uint32_t r0[4], r1[4];
+        dw_row<KS>(0, y, w, bd, r0);
+        dw_row<KS>(1, y, w, bd, r1);
+        TR_MARK(2, 4);
+        tr_wait_empty(&bars[TB_Z_EMPTY], z_n);  // pw2 of the previous chunk has consumed Z
+        TR_MARK(2, 5);
+        store_row(0, r0);
+        store_row(1, r1);
+        dw_row<KS>(2, y, w, bd, r0);
+        store_row(2, r0);
+        dw_row<KS>(3, y, w, bd, r1);
+        store_row(3, r1);
+    } else {
+        uint32_t packed[4][4];
+#pragma unroll
+        for (int lo = 0; lo < 4; ++lo) dw_row<KS>(lo, y, w, bd, packed[lo]);
+        TR_MARK(2, 4);
+        tr_wait_empty(&bars[TB_Z_EMPTY], z_n);  // pw2 of the previous chunk has consumed Z
+        TR_MARK(2, 5);
+#pragma unroll
+        for (int lo = 0; lo < 4; ++lo) store_row(lo, packed[lo]);
     }
     fence_proxy_async_smem();
     __syncwarp();

@@ -1,4 +1,4 @@
-// Probe: cycles of dw_half<KS> (hm_trunk.cuh) alone, 16 warps per CTA on every SM: is the in-kernel depthwise
+// Probe: cycles of the four dw_row<KS> calls of a chunk (hm_trunk.cuh) alone, 16 warps per CTA on every SM: is the in-kernel depthwise
 // (5x5: ~4300 cycles per chunk, 3x3: ~1560) slow by itself or by interference?  FMA-pipe floors: 2448 / 1056.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o probe_dwhalf probe_dwhalf.cu
 #include <cstdio>
@@ -16,10 +16,11 @@ __global__ void __launch_bounds__(640, 1) k(const float* in, float* out, long lo
     __syncthreads();
     const long long t0 = clock64();
     for (int it = 0; it < iters; ++it) {
-        uint32_t packed[16];
-        dw_half<KS>(y, w, in[it & 1023], packed);
+        uint32_t packed[4][4];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) acc ^= packed[j];
+        for (int lo = 0; lo < 4; ++lo) dw_row<KS>(lo, y, w, in[it & 1023], packed[lo]);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc ^= packed[j >> 2][j & 3];
         y[it & 7] += __uint_as_float(acc & 0x3f800000u) * 1e-9f;   // keep the loop honest
     }
     __syncthreads();
