@@ -36,6 +36,7 @@ class RootPolicy(C.Structure):  # hm_root_policy
     ]
 
 
+ROOT_NOALLOC_MAX_MOVES = 1 << 20  # HM_ROOT_NOALLOC_MAX_MOVES
 ROOT_OK, ROOT_RESAMPLED, ROOT_RESAMPLED_FORCED = 0, 1, 2
 ROOT_EMPTY_LIST, ROOT_BAD_WEIGHTS, ROOT_NO_LEGAL_JOINT = -1, -2, -3
 
@@ -62,6 +63,7 @@ SYMBOLS = {
     "hm_engine_enqueue_positions": (_i, [_vp, _vp, _sz, _vp, _vp, _sz]),
     "hm_engine_sync_priors": (_i, [_vp, _sz, _pp, _pp, _pp]),
     "hm_root_policy_apply": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, C.POINTER(RootPolicy), _vp, _vp, _vp]),
+    "hm_root_policy_apply_noalloc": (_i, [_i, _vp, _sz, _vp, _vp, _sz, _vp, C.POINTER(RootPolicy), _vp, _vp, _vp]),
     "hm_engine_enqueue_positions_root": (_i, [_vp, _vp, _sz, _vp, _vp, C.POINTER(RootPolicy), _sz]),
     "hm_engine_sync_root": (_i, [_vp, _sz, _pp, _pp, _pp, _pp, _pp]),
     "hm_engine_set_value_config": (C.c_int, [_vp, C.POINTER(ValueConfig)]),

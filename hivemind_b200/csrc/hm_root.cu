@@ -8,7 +8,10 @@
 // picks are bit-identical to the host code; the per-move work (pow, gamma variates, the mix) is spread
 // over the lanes.
 #include <math.h>
+#include <mutex>
+#include <string>
 #include "hm_kernels.h"
+#include "hm_net.h"   // set_error / cuda_ok
 
 namespace hm {
 
@@ -191,3 +194,76 @@ void launch_root_policy(const hm_packed_pos* pos, int n_pos, const uint32_t* mov
 }
 
 }  // namespace hm
+
+// ---- allocation-free entry point (include/hm_engine.h: hm_root_policy_apply_noalloc) ---------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The only scratch
+// root_policy_kernel needs — the Gamma variates of the Dirichlet-noise stage, one float per move — lives in this
+// file-scope device array instead of a cudaMalloc'ed buffer.  Every GPU that loads the library holds its 4 MiB until
+// the process exits.  In HOST code `g_noalloc_noise` is only a stand-in for the symbol, never a device address: the
+// address a kernel may be given is resolved per device with cudaGetSymbolAddress below.
+static __device__ __align__(256) float g_noalloc_noise[HM_ROOT_NOALLOC_MAX_MOVES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+float* g_noalloc_ptr[kMaxDevices] = {};   // per device: the device address of g_noalloc_noise on THAT device
+
+// Resolved once per device, with that device current.
+float* noalloc_scratch(int device) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[device] == nullptr) {
+        void* p = nullptr;
+        if (!hm::cuda_ok(cudaGetSymbolAddress(&p, g_noalloc_noise), "cudaGetSymbolAddress(noalloc scratch)")) return nullptr;
+        g_noalloc_ptr[device] = static_cast<float*>(p);
+    }
+    return g_noalloc_ptr[device];
+}
+}  // namespace
+
+extern "C" int hm_root_policy_apply_noalloc(int device, const hm_packed_pos* d_pos, size_t n_pos,
+                                            const uint32_t* d_moves, const uint32_t* d_move_offsets, size_t n_moves,
+                                            float* d_priors, const hm_root_policy* rp, uint32_t* d_picks,
+                                            int32_t* d_status, void* stream) {
+    try {
+        if (!d_pos || !d_move_offsets || !d_priors) { hm::set_error("null argument"); return 0; }
+        if (!rp) { hm::set_error("null root policy"); return 0; }
+        if (rp->temperature < 0.0 || rp->temperature != rp->temperature) {
+            hm::set_error("Policy temperature must be positive");  // selfplay.cc:168-170
+            return 0;
+        }
+        if (device < 0 || device >= kMaxDevices) { hm::set_error("no such CUDA device"); return 0; }
+        if (n_moves > HM_ROOT_NOALLOC_MAX_MOVES) {
+            hm::set_error("hm_root_policy_apply_noalloc: " + std::to_string(n_moves) + " moves exceed HM_ROOT_NOALLOC_MAX_MOVES (" +
+                          std::to_string(HM_ROOT_NOALLOC_MAX_MOVES) + "), the size of the static scratch array");
+            return 0;
+        }
+        if (n_pos > 0x7fffffffu / 32u) { hm::set_error("too many positions"); return 0; }
+        if (n_moves > 0 && !d_moves) { hm::set_error("null move list"); return 0; }
+        if (n_pos == 0) return 1;
+        int current = -1;
+        if (!hm::cuda_ok(cudaGetDevice(&current), "cudaGetDevice")) return 0;
+        if (current != device && !hm::cuda_ok(cudaSetDevice(device), "cudaSetDevice")) return 0;
+        float* noise = noalloc_scratch(device);
+        if (!noise) return 0;
+        hm::RootPolicyArgs a;
+        a.temperature = rp->temperature;
+        a.alpha = rp->dirichlet_alpha;
+        a.epsilon = rp->dirichlet_epsilon;
+        a.seed = rp->noise_seed;
+        a.hash = rp->position_hash;   // DEVICE pointers for this entry point
+        a.captures = rp->captures;
+        a.uniforms = rp->uniforms;
+        // Nothing in the scratch has to start at zero: a warp writes the variates of its own lists before it reads
+        // them, and lists the noise stage skips are never read.  The array keeps the previous call's contents.
+        hm::launch_root_policy(d_pos, static_cast<int>(n_pos), d_moves, d_move_offsets, d_priors, a, noise, d_picks, d_status,
+                               static_cast<cudaStream_t>(stream));
+        return hm::cuda_ok(cudaGetLastError(), "root policy kernel (noalloc)") ? 1 : 0;
+    } catch (const std::exception& ex) {
+        hm::set_error(std::string("exception: ") + ex.what());
+        return 0;
+    } catch (...) {
+        hm::set_error("unknown exception");
+        return 0;
+    }
+}

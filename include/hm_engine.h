@@ -210,6 +210,28 @@ int hm_engine_enqueue_positions_root(hm_engine* e, const hm_packed_pos* pos, siz
 int hm_engine_sync_root(hm_engine* e, size_t worker, const float** priors, const float** values,
                         const float** raw, const uint32_t** picks, const int32_t** status);
 
+/* Allocation-free variant of hm_root_policy_apply.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  It calls no cudaMalloc / cudaFree / allocating library routine, copies nothing and does
+ * not synchronise: it launches the root-policy kernel on `stream` (a cudaStream_t; NULL = the default stream) of
+ * `device` and returns.
+ *   - every buffer is the CALLER's DEVICE memory: d_pos [n_pos], d_moves [n_moves], d_move_offsets [2*n_pos+1]
+ *     (non-decreasing, d_move_offsets[2*n_pos] == n_moves: not checked, they are not readable from the host here),
+ *     d_priors [n_moves] (updated in place), d_picks [n_pos][2] / d_status [n_pos] (may be NULL), and the three
+ *     pointers inside *rp (position_hash, captures, uniforms — DEVICE pointers here; the struct itself is host memory);
+ *   - the kernel's scratch (one Gamma variate per move for the Dirichlet-noise stage) is a static device array of
+ *     HM_ROOT_NOALLOC_MAX_MOVES floats (4 MiB) that every GPU which loads the library holds until the process exits;
+ *     n_moves beyond that limit is refused with an error.  The first call on a device resolves the array's device
+ *     address (cudaGetSymbolAddress): make it once outside stream capture;
+ *   - all calls on a device share that array, which keeps the previous call's contents (nothing in it has to start at
+ *     zero: the kernel writes every variate before it reads it).  Two calls whose kernels overlap on the GPU (different
+ *     streams, no dependency) RACE on it: order them on one stream or with events.
+ * Returns 1 / 0 (hm_last_error) like hm_root_policy_apply; results are bit-identical to that entry point's. */
+#define HM_ROOT_NOALLOC_MAX_MOVES (1u << 20)
+int hm_root_policy_apply_noalloc(int device, const hm_packed_pos* d_pos, size_t n_pos, const uint32_t* d_moves,
+                                 const uint32_t* d_move_offsets, size_t n_moves, float* d_priors,
+                                 const hm_root_policy* rp, uint32_t* d_picks, int32_t* d_status, void* stream);
+
 /* ---- stand-alone stages (parity checks and benches) ---------------------------- */
 
 /* board_to_planes for n packed positions -> [n,74,8,8] of `dtype` in HOST memory
