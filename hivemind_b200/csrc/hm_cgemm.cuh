@@ -42,6 +42,8 @@ struct CgemmParams {
     const act_t* residual;  // optional [pos][out_channels][64], added before the activation
     int ksteps_last;    // valid 16-channel K steps (1..8) in the last 128-channel K pair: the rest is zero padding
     int stages;         // ring depth (1..CG_STAGES); shallow-K 1x1 layers use 1 so that 3 CTAs share an SM
+    int n_items;        // cconv3_kernel (hm_cconv.cuh): (position tile, 128-row output block) work items
+    int trace;          // -DHM_BRINGUP builds only: CTA 0 of a cconv3_kernel launch logs its timeline
 };
 
 constexpr int CG_THREADS = 192;

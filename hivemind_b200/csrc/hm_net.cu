@@ -10,6 +10,7 @@
 #include <mutex>
 
 #include "hm_cgemm.cuh"
+#include "hm_cconv.cuh"
 #include "hm_lgemm.cuh"
 #include "hm_pgemm.cuh"
 #include "hm_trunk.cuh"
@@ -489,6 +490,8 @@ static bool kernels_prepare() {
     std::call_once(once, []() {
         ok = cuda_ok(cudaFuncSetAttribute(cgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CG_SMEM),
                      "cudaFuncSetAttribute(cgemm)") &&
+             cuda_ok(cudaFuncSetAttribute(cconv3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CC_SMEM),
+                     "cudaFuncSetAttribute(cconv3)") &&
              cuda_ok(cudaFuncSetAttribute(trunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM),
                      "cudaFuncSetAttribute(trunk)") &&
              cuda_ok(cudaFuncSetAttribute(lgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -612,6 +615,19 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
         op.launch = [p, tm_w, tm_x, lgrid, lsmem, n_tiles](cudaStream_t s) {
             lgemm_kernel<<<lgrid, LG_THREADS, lsmem, s>>>(p, n_tiles, tm_w, tm_x);
         };
+        ops.push_back(std::move(op));
+        return true;
+    }
+    // 3x3 layers: one persistent CTA per SM walks the (tile, output block) work items (hm_cconv.cuh); HM_NO_CCONV=1 opts out
+    if (L.ksize == 3 && p.residual == nullptr && getenv("HM_NO_CCONV") == nullptr) {
+        p.n_items = grid;
+#ifdef HM_BRINGUP
+        if (const char* t = getenv("HM_CG_TRACE")) p.trace = (L.name + io.suffix) == t ? 1 : 0;
+#endif
+        int n_sm = 148;
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
+        const int cgrid = std::min(grid, n_sm);
+        op.launch = [p, tm_w, tm_x, cgrid](cudaStream_t s) { cconv3_kernel<<<cgrid, CC_THREADS, CC_SMEM, s>>>(p, tm_w, tm_x); };
         ops.push_back(std::move(op));
         return true;
     }
@@ -1014,3 +1030,12 @@ void engine_free_workers(Engine* e) {
 }
 
 }  // namespace hm
+
+#ifdef HM_BRINGUP
+// bring-up only: the timeline CTA 0 of the traced cgemm launch (HM_CG_TRACE=<op name>) wrote; 3 roles x CG_TRACE_CAP
+extern "C" int hm_debug_cg_trace(unsigned long long* out, int cap) {
+    if (cap < 3 * hm::CC_TRACE_CAP) return 0;
+    if (cudaDeviceSynchronize() != cudaSuccess) return 0;
+    return cudaMemcpyFromSymbol(out, hm::g_cc_trace, sizeof(unsigned long long) * 3 * hm::CC_TRACE_CAP) == cudaSuccess ? 1 : 0;
+}
+#endif

@@ -1,7 +1,7 @@
 // hm_planes.cu — stage P: packed bughouse positions -> input planes, on device.
 // Mirrors board_to_planes_impl (reference engine/src/environment/planes.cc:213-257) value for
 // value; the channel order is planes.cc:236-256 and is cross-checked bit-exactly against the
-// reference-compiled oracle (tests/test_planes_gpu.py).
+// reference-compiled oracle (tests/test_gpu_planes_policy.py).
 #include <stddef.h>
 #include "hm_kernels.h"
 #include "hm_ptx.cuh"

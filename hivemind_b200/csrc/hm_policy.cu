@@ -117,6 +117,8 @@ __device__ __forceinline__ int warp_sum_i(int v) {
     return v;
 }
 
+constexpr int PRI_REG = 4;   // moves per lane held in registers by the short-list path
+
 template <typename L>
 __global__ void __launch_bounds__(128)
 policy_priors_kernel(L logits, const hm_packed_pos* __restrict__ pos, int n_pos,
@@ -131,6 +133,62 @@ policy_priors_kernel(L logits, const hm_packed_pos* __restrict__ pos, int n_pos,
     if (n <= 0) return;
     const int stm_black = (pos[p].board[board].flags & HM_FLAG_STM_BLACK) ? 1 : 0;
     const float NEG_INF = -INFINITY;
+
+    if (n <= 32 * PRI_REG) {
+        // Lists of up to 128 moves (every list of the golden positions; bughouse lists beyond that are rare) stay in
+        // registers: offsets | flags -> moves -> logits -> priors are the only dependent global round trips, the
+        // loads of a round are all in flight together, and nothing is staged through `priors`.  The arithmetic is the
+        // long-list path's, operation for operation.
+        float l[PRI_REG];
+        uint32_t mv[PRI_REG];
+#pragma unroll
+        for (int k = 0; k < PRI_REG; ++k) mv[k] = lane + 32 * k < n ? __ldg(moves + lo + lane + 32 * k) : 0u;
+        float mx = NEG_INF;
+        int finite = 0;
+#pragma unroll
+        for (int k = 0; k < PRI_REG; ++k) {
+            l[k] = NEG_INF;
+            if (lane + 32 * k < n) {
+                const int idx = policy_index(mv[k], stm_black);
+                if (idx >= 0) l[k] = logits.at(p, board, idx);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < PRI_REG; ++k)
+            if (isfinite(l[k])) { mx = fmaxf(mx, l[k]); ++finite; }
+        mx = warp_max(mx);
+        if (!isfinite(mx)) {  // utils.h:136-141
+            const float u = 1.0f / static_cast<float>(n);
+#pragma unroll
+            for (int k = 0; k < PRI_REG; ++k)
+                if (lane + 32 * k < n) priors[lo + lane + 32 * k] = u;
+            return;
+        }
+        double sum = 0.0;
+        float e[PRI_REG];
+#pragma unroll
+        for (int k = 0; k < PRI_REG; ++k) {
+            e[k] = 0.0f;
+            if (isfinite(l[k])) {
+                e[k] = static_cast<float>(exp(static_cast<double>(l[k] - mx)));
+                sum += static_cast<double>(e[k]);
+            }
+        }
+        // the long-list path adds lane-strided partial sums in the same order: i = lane, lane + 32, ...
+        sum = warp_sum_d(sum);
+        if (!isfinite(sum) || sum <= 0.0) {  // utils.h:151-161
+            finite = warp_sum_i(finite);
+            const float u = finite > 0 ? 1.0f / static_cast<float>(finite) : 0.0f;
+#pragma unroll
+            for (int k = 0; k < PRI_REG; ++k)
+                if (lane + 32 * k < n) priors[lo + lane + 32 * k] = isfinite(l[k]) ? u : 0.0f;
+            return;
+        }
+#pragma unroll
+        for (int k = 0; k < PRI_REG; ++k)  // utils.h:163-165
+            if (lane + 32 * k < n) priors[lo + lane + 32 * k] = static_cast<float>(static_cast<double>(e[k]) / sum);
+        return;
+    }
 
     // pass 1: gather, max over finite logits (utils.h:129-134)
     float mx = NEG_INF;

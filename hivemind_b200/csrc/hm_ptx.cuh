@@ -69,6 +69,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
 }
+// for long waits of many warps (an epilogue waiting for a whole mainloop): the pollers stay off the issue slots and the
+// shared-memory port the MMA issuer and the tensor pipe are using
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity, unsigned ns) {
+    while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+}
 
 // ---- TMA ------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
@@ -206,6 +211,34 @@ __device__ __forceinline__ void umma_f16_burst8(uint32_t d_tmem, uint32_t a_lo, 
           "n"(UMMA_DESC_HI_SW128), "n"(IDESC)
         : "memory");
 #undef HM_MMA_STEP
+}
+// The same burst with a run-time K-step count nk (1..8): steps k >= nk are skipped by a guard predicate (the last
+// 128-channel pair of a layer whose channel count is not a multiple of 128); both commits are always issued, so the
+// barrier protocol does not depend on nk.
+template <int AJ, int AK, int BJ, int BK, uint32_t IDESC>
+__device__ __forceinline__ void umma_f16_burst8n(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t acc_first,
+                                                 uint32_t nk, uint64_t* bar_tile0, uint64_t* bar_tile1) {
+#define HM_MMA_STEPG(K, AOFF, BOFF)                                               \
+    "setp.gt.u32 g, %6, " #K ";\n\t"                                              \
+    "add.u32 ta, %1, " #AOFF ";\n\t add.u32 tb, %2, " #BOFF ";\n\t"              \
+    "mov.b64 da, {ta, %21};\n\t mov.b64 db, {tb, %21};\n\t"                       \
+    "@g tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %22, q;\n\t"
+    asm volatile(
+        "{\n\t.reg .pred p, q, g;\n\t.reg .b64 da, db;\n\t.reg .b32 ta, tb;\n\t"
+        "setp.ne.b32 p, %3, 0;\n\t setp.eq.b32 q, %0, %0;\n\t"
+        "mov.b64 da, {%1, %21};\n\t mov.b64 db, {%2, %21};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %22, p;\n\t"
+        HM_MMA_STEPG(1, %7, %8) HM_MMA_STEPG(2, %9, %10) HM_MMA_STEPG(3, %11, %12)
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%4];\n\t"
+        HM_MMA_STEPG(4, %13, %14) HM_MMA_STEPG(5, %15, %16) HM_MMA_STEPG(6, %17, %18) HM_MMA_STEPG(7, %19, %20)
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%5];\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(acc_first),
+          "r"(smem_u32(bar_tile0)), "r"(smem_u32(bar_tile1)), "r"(nk),
+          "n"(AK), "n"(BK), "n"(2 * AK), "n"(2 * BK), "n"(3 * AK), "n"(3 * BK),
+          "n"(AJ), "n"(BJ), "n"(AJ + AK), "n"(BJ + BK), "n"(AJ + 2 * AK), "n"(BJ + 2 * BK), "n"(AJ + 3 * AK), "n"(BJ + 3 * BK),
+          "n"(UMMA_DESC_HI_SW128), "n"(IDESC)
+        : "memory");
+#undef HM_MMA_STEPG
 }
 // Arrive on an mbarrier when all previously issued tcgen05.mma of this thread completed.
 // (implies tcgen05.fence::before_thread_sync)
