@@ -671,6 +671,22 @@ static bool add_narrow_io(std::vector<Op>& ops, const DenseLayer& L, const Dense
     op.klass = "dense";
     op.flops = 2.0 * L.macs_per_pos() * io.in_n;
     op.bytes = 0;
+    // persistent version (one CTA per SM walks the tiles, trunk-style issue loop, 16 epilogue warps); HM_NO_PCONV=1 opts out
+    if ((npad == 160 || npad == 80) && getenv("HM_NO_PCONV") == nullptr) {
+        static bool pc_attr_set = false;
+        if (!pc_attr_set) {
+            if (!cuda_ok(cudaFuncSetAttribute(pconv3_kernel<160>, cudaFuncAttributeMaxDynamicSharedMemorySize, pc_smem_bytes(160)), "pconv3<160> smem attr") ||
+                !cuda_ok(cudaFuncSetAttribute(pconv3_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, pc_smem_bytes(80)), "pconv3<80> smem attr")) return false;
+            pc_attr_set = true;
+        }
+        int n_sm = 148;
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
+        const int n_tiles = grid, cgrid = std::min(grid, n_sm);
+        if (npad == 160) op.launch = [p, tm_w, tm_x, cgrid, n_tiles](cudaStream_t s) { pconv3_kernel<160><<<cgrid, PC_THREADS, pc_smem_bytes(160), s>>>(p, n_tiles, tm_w, tm_x); };
+        else op.launch = [p, tm_w, tm_x, cgrid, n_tiles](cudaStream_t s) { pconv3_kernel<80><<<cgrid, PC_THREADS, pc_smem_bytes(80), s>>>(p, n_tiles, tm_w, tm_x); };
+        ops.push_back(std::move(op));
+        return true;
+    }
     op.launch = [p, tm_w, tm_x, grid, smem](cudaStream_t s) { pgemm_kernel<<<grid, PG_THREADS, smem, s>>>(p, tm_w, tm_x); };
     ops.push_back(std::move(op));
     return true;

@@ -217,4 +217,201 @@ pgemm_kernel(const PgemmParams p, const __grid_constant__ CUtensorMap tmW, const
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// pconv3_kernel<NPAD> — the same convolution driven like cconv3_kernel (hm_cconv.cuh): ONE persistent CTA per SM walks
+// the position tiles; the MMA issuer is the trunk's fully unrolled burst loop (ring slots and barriers are compile-time
+// offsets of uniform registers; with run-time ring indices a burst of 8 MMAs took ~1.4x its tensor time); weights
+// stream through six [NPAD rows x 64 K] tiles with pair-full / tile-empty barriers, activations through three 32 KB
+// stages loaded by a warp of their own (it has to keep loading while the epilogue of the previous tile runs);
+// sixteen epilogue warps (four per TMEM lane quarter) share the 16-column chunks of the three accumulators.
+// Warps: 0 weight producer, 1 MMA issuer + TMEM owner, 2 activation producer, 3 idle, 4-19 epilogue.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int PC_EPI_WARPS = 16;
+constexpr int PC_THREADS = 128 + PC_EPI_WARPS * 32;
+constexpr int PC_XSTAGES = 3;
+__host__ __device__ constexpr int pc_tile_bytes(int npad) { return npad * 128; }
+__host__ __device__ constexpr int pc_x_off(int npad) { return 6 * pc_tile_bytes(npad); }
+__host__ __device__ constexpr int pc_bar_off(int npad) { return pc_x_off(npad) + PC_XSTAGES * PG_XSTAGE_BYTES; }
+__host__ __device__ constexpr int pc_smem_bytes(int npad) { return pc_bar_off(npad) + 256 + 1024; }
+enum {
+    PB_X_FULL = 0, PB_X_EMPTY = PB_X_FULL + PC_XSTAGES, PB_PAIR_FULL = PB_X_EMPTY + PC_XSTAGES,
+    PB_TILE_EMPTY = PB_PAIR_FULL + 3, PB_ACCUM = PB_TILE_EMPTY + 6, PB_DRAINED = PB_ACCUM + 1, PB_COUNT = PB_DRAINED + 1
+};
+
+template <int NPAD>
+__global__ void __launch_bounds__(PC_THREADS, 1)
+pconv3_kernel(const PgemmParams p, const int n_tiles, const __grid_constant__ CUtensorMap tmW,
+              const __grid_constant__ CUtensorMap tmX) {
+    static_assert(NPAD % 16 == 0 && NPAD <= 160, "three accumulators of NPAD columns must fit 512 TMEM columns");
+    extern __shared__ uint8_t pc_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(pc_smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    constexpr int TILE = pc_tile_bytes(NPAD);
+    uint8_t* smem_x = smem + pc_x_off(NPAD);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + pc_bar_off(NPAD));
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + PB_COUNT);
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmW);
+        tma_prefetch_desc(&tmX);
+        for (int i = 0; i < PB_COUNT; ++i) mbar_init(&bars[i], i == PB_DRAINED ? PC_EPI_WARPS : 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int kpairs = p.kblocks >> 1;
+
+    if (warp == 0) {
+        // ===== weight producer =====
+        const bool leader = elect_one();
+        const int tap_cols = p.kblocks * 64;
+        uint32_t wk = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            int ky = 0, kp = 0;
+            for (int step = 0; step < 3 * kpairs; ++step, ++wk) {
+                const bool upper = kp + 1 < kpairs || p.ksteps_last > 4;
+#pragma unroll
+                for (int kx = 0; kx < 3; ++kx) {
+                    const int kcol = (ky * 3 + kx) * tap_cols + kp * 128;
+                    mbar_wait(&bars[PB_TILE_EMPTY + 2 * kx], (wk & 1) ^ 1);
+                    if (leader) {
+                        mbar_arrive_expect_tx(&bars[PB_PAIR_FULL + kx], upper ? 2 * TILE : TILE);
+                        tma_load_2d(smem + (2 * kx) * TILE, &tmW, &bars[PB_PAIR_FULL + kx], kcol, 0);
+                    }
+                    __syncwarp();
+                    mbar_wait(&bars[PB_TILE_EMPTY + 2 * kx + 1], (wk & 1) ^ 1);
+                    if (leader && upper) tma_load_2d(smem + (2 * kx + 1) * TILE, &tmW, &bars[PB_PAIR_FULL + kx], kcol + 64, 0);
+                    __syncwarp();
+                }
+                if (++kp == kpairs) { kp = 0; ++ky; }
+            }
+        }
+    } else if (warp == 2) {
+        // ===== activation producer =====
+        const bool leader = elect_one();
+        uint32_t xk = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            int ky = 0, kp = 0;
+            for (int s3 = 0; s3 < kpairs; ++s3, ++xk) {
+#pragma unroll
+                for (int u = 0; u < PC_XSTAGES; ++u) {
+                    const bool upper = kp + 1 < kpairs || p.ksteps_last > 4;
+                    mbar_wait(&bars[PB_X_EMPTY + u], (xk & 1) ^ 1);
+                    if (leader) {
+                        uint8_t* dst = smem_x + u * PG_XSTAGE_BYTES;
+                        mbar_arrive_expect_tx(&bars[PB_X_FULL + u], upper ? PG_XSTAGE_BYTES : PG_XSTAGE_BYTES / 2);
+                        tma_load_3d(dst, &tmX, &bars[PB_X_FULL + u], 8 * (ky - 1), kp * 128, tile * 2);
+                        if (upper) tma_load_3d(dst + 16384, &tmX, &bars[PB_X_FULL + u], 8 * (ky - 1), kp * 128 + 64, tile * 2);
+                    }
+                    __syncwarp();
+                    if (++kp == kpairs) { kp = 0; ++ky; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: A = activations MN-major (idesc bit 15), B = weights K-major =====
+        const bool leader = elect_one();
+        constexpr uint32_t idesc = umma_idesc_16(128, NPAD, UMMA_FMT_16) | (1u << 15);
+        const uint32_t w_lo = static_cast<uint32_t>(umma_desc_sw128(smem_u32(smem)));
+        const uint32_t x_lo = static_cast<uint32_t>(umma_desc_mn_sw128(smem_u32(smem_x), 8192, 1024));
+        uint32_t xpar = 0, wpar = 0, have = 0, it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+            if (it > 0) {   // the epilogue warps have read the previous tile's accumulators
+                mbar_wait(&bars[PB_DRAINED], (it - 1) & 1);
+                tc_fence_after();
+            }
+            int kp = 0;
+            uint32_t acc0 = 0;
+            for (int s3 = 0; s3 < kpairs; ++s3) {
+#pragma unroll
+                for (int u = 0; u < PC_XSTAGES; ++u) {
+                    const uint32_t nk = kp + 1 < kpairs ? 8u : static_cast<uint32_t>(p.ksteps_last);
+                    mbar_wait(&bars[PB_X_FULL + u], xpar);
+#pragma unroll
+                    for (int kx = 0; kx < 3; ++kx) {
+                        if (kx == 0 && !have) mbar_wait(&bars[PB_PAIR_FULL], wpar);
+                        tc_fence_after();
+                        const int nb = kx == 2 ? 0 : kx + 1;
+                        const uint32_t npar = kx == 2 ? wpar ^ 1 : wpar;
+                        const uint32_t next_ok = mbar_test_wait(&bars[PB_PAIR_FULL + nb], npar);
+                        if (leader) {
+                            umma_f16_burst8n<1024, 128, TILE / 16, 2, idesc>(tmem_base + kx * NPAD, x_lo + u * (PG_XSTAGE_BYTES / 16),
+                                                                             w_lo + (2 * kx) * (TILE / 16), acc0, nk,
+                                                                             &bars[PB_TILE_EMPTY + 2 * kx], &bars[PB_TILE_EMPTY + 2 * kx + 1]);
+                            if (kx == 2) umma_commit(&bars[PB_X_EMPTY + u]);
+                        }
+                        __syncwarp();
+                        if (kx < 2) {
+                            if (!next_ok) mbar_wait(&bars[PB_PAIR_FULL + nb], npar);
+                        } else {
+                            have = next_ok;
+                        }
+                    }
+                    wpar ^= 1;
+                    acc0 = 1;
+                    if (++kp == kpairs) kp = 0;
+                }
+                xpar ^= 1;
+            }
+            if (leader) umma_commit(&bars[PB_ACCUM]);
+            __syncwarp();
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue: thread = one square of one position; warp = (lane quarter q, chunk group g) =====
+        const int q = warp & 3;
+        const int g = (warp - 4) >> 2;
+        const int m = q * 32 + lane;                 // TMEM lane = row of D
+        const int sq = m & 63;
+        const bool has_left = (sq & 7) != 0, has_right = (sq & 7) != 7;
+        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        constexpr int CHUNKS = NPAD / 16;
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+            const int pos = tile * 2 + (m >> 6);
+            const size_t out_base = static_cast<size_t>(pos) * p.out_channels * 64 + sq;
+            mbar_wait_backoff(&bars[PB_ACCUM], it & 1, 64);
+            tc_fence_after();
+#pragma unroll 1
+            for (int ci = g; ci < CHUNKS; ci += 4) {
+                const int c0 = ci * 16;
+                uint32_t l[16], c[16], r[16];
+                tmem_ld_32x32b_x16(t_row + c0, l);                 // P_-1
+                tmem_ld_32x32b_x16(t_row + NPAD + c0, c);          // P_0
+                tmem_ld_32x32b_x16(t_row + 2 * NPAD + c0, r);      // P_+1
+                tmem_ld_wait();
+                if (ci + 4 >= CHUNKS) {   // this warp's last TMEM read of the tile
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&bars[PB_DRAINED]);
+                }
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float fl = __shfl_up_sync(0xffffffffu, __uint_as_float(l[j]), 1);     // square x-1 (same rank)
+                    const float fr = __shfl_down_sync(0xffffffffu, __uint_as_float(r[j]), 1);   // square x+1
+                    const int ch = c0 + j;
+                    if (ch >= p.n_valid) continue;    // warp-uniform
+                    float v = __uint_as_float(c[j]) + (has_left ? fl : 0.0f) + (has_right ? fr : 0.0f);
+                    if (p.bias != nullptr) v += __ldg(p.bias + ch);
+                    if (p.relu == 1) v = fmaxf(v, 0.0f);
+                    const size_t o = out_base + static_cast<size_t>(ch) * 64;
+                    if (p.out_f32) static_cast<float*>(p.out)[o] = v;
+                    else static_cast<act_t*>(p.out)[o] = float_to_act(v);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
 }  // namespace hm
