@@ -54,8 +54,16 @@ enum {
     CB_COUNT = CB_DRAINED + 1
 };
 
+// PACKED (layers with 64 < cin <= 80, i.e. the stem's 74 planes): a tap costs 80 K values, not 128.  Per horizontal
+// tap kx the K dimension is four 64-row tiles, T0-T2 = channels 0-63 at ky = 0, 1, 2 and T3 = channels 64-79 of the
+// three ky stacked (48 rows), i.e. TWO steps per item — (T0 | T1) with 8 K steps and (T2 | T3) with 7 — instead of
+// three steps that each load 128 K values of which 80 are real: 246 KB instead of 384 KB through the ~64 B/clk
+// per-SM ingest for 45 MMAs.  The weight matrix is packed to match ([n_rows][kx][256], hm_net.cu pack_conv_tap_packed),
+// T3 is gathered by six 2 KB boxes (tmX16: 16 channels x 1 position).
+template <bool PACKED>
 __global__ void __launch_bounds__(CC_THREADS, 1)
-cconv3_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX) {
+cconv3_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
+              const __grid_constant__ CUtensorMap tmX16) {
     extern __shared__ uint8_t cc_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cc_smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + CC_BAR_OFF);
@@ -90,6 +98,45 @@ cconv3_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW, cons
             const int tile = item / p.m_blocks;
             const int row0 = (item - tile * p.m_blocks) * 128, pos0 = tile * 2;
             CC_MARK(0, 1);
+            if constexpr (PACKED) {
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    mbar_wait(&bars[CB_X_EMPTY + u], (xk & 1) ^ 1);
+                    if (leader) {
+                        uint8_t* dst = smem + CC_X_OFF + u * CG_STAGE_BYTES;
+                        if (u == 0) {
+                            mbar_arrive_expect_tx(&bars[CB_X_FULL], CG_STAGE_BYTES);
+                            tma_load_3d(dst, &tmX, &bars[CB_X_FULL], -8, 0, pos0);
+                            tma_load_3d(dst + 16384, &tmX, &bars[CB_X_FULL], 0, 0, pos0);
+                        } else {
+                            mbar_arrive_expect_tx(&bars[CB_X_FULL + 1], 16384 + 6 * 2048);
+                            tma_load_3d(dst, &tmX, &bars[CB_X_FULL + 1], 8, 0, pos0);
+#pragma unroll
+                            for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+                                for (int pp = 0; pp < 2; ++pp)
+                                    tma_load_3d(dst + 16384 + pp * 8192 + ky * 2048, &tmX16, &bars[CB_X_FULL + 1], 8 * (ky - 1), 64, pos0 + pp);
+                        }
+                    }
+                    __syncwarp();
+#pragma unroll
+                    for (int kx = 0; kx < 3; ++kx) {
+                        const int kcol = kx * 256 + u * 128;
+                        mbar_wait(&bars[CB_TILE_EMPTY + 2 * kx], (wk & 1) ^ 1);
+                        if (leader) {
+                            mbar_arrive_expect_tx(&bars[CB_PAIR_FULL + kx], CG_STAGE_BYTES);
+                            tma_load_2d(smem + (2 * kx) * 16384, &tmW, &bars[CB_PAIR_FULL + kx], kcol, row0);
+                        }
+                        __syncwarp();
+                        mbar_wait(&bars[CB_TILE_EMPTY + 2 * kx + 1], (wk & 1) ^ 1);
+                        if (leader) tma_load_2d(smem + (2 * kx + 1) * 16384, &tmW, &bars[CB_PAIR_FULL + kx], kcol + 64, row0);
+                        __syncwarp();
+                    }
+                    ++wk;
+                }
+                ++xk;
+                continue;
+            }
             int ky = 0, kp = 0;
             for (int s3 = 0; s3 < kpairs; ++s3, ++xk) {
 #pragma unroll
@@ -139,10 +186,10 @@ cconv3_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW, cons
             CC_MARK(1, 2);
             int kp = 0;
             uint32_t acc0 = 0;   // 0 on the first step of the item: the bursts overwrite the accumulators
-            for (int s3 = 0; s3 < kpairs; ++s3) {
+            for (int s3 = 0; s3 < (PACKED ? 1 : kpairs); ++s3) {
 #pragma unroll
-                for (int u = 0; u < CC_XSTAGES; ++u) {
-                    const uint32_t nk = kp + 1 < kpairs ? 8u : static_cast<uint32_t>(p.ksteps_last);
+                for (int u = 0; u < (PACKED ? 2 : CC_XSTAGES); ++u) {
+                    const uint32_t nk = PACKED ? (u == 0 ? 8u : 7u) : kp + 1 < kpairs ? 8u : static_cast<uint32_t>(p.ksteps_last);
                     mbar_wait(&bars[CB_X_FULL + u], xpar);
                     CC_MARK(1, 3);
 #pragma unroll

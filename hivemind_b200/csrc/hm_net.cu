@@ -107,10 +107,10 @@ static bool make_tm_weights(CUtensorMap* tm, const void* w, size_t rows, int kco
 // channels x 2 positions = one MN-major B-operand block (also the trunk's tile load / store).
 // A box shifted by +-8 squares reads zeros off the board, one shifted beyond the last channel
 // reads zeros too (convolution padding and K padding for free).
-static bool make_tm_act3(CUtensorMap* tm, const void* x, int n, int C, int pos_stride_ch = 0) {
+static bool make_tm_act3(CUtensorMap* tm, const void* x, int n, int C, int pos_stride_ch = 0, int box_ch = 64, int box_pos = 2) {
     cuuint64_t dims[3] = {64, static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(n)};
     cuuint64_t strides[2] = {128, static_cast<cuuint64_t>(pos_stride_ch ? pos_stride_ch : C) * 128};
-    cuuint32_t box[3] = {64, 64, 2};
+    cuuint32_t box[3] = {64, static_cast<cuuint32_t>(box_ch), static_cast<cuuint32_t>(box_pos)};
     cuuint32_t es[3] = {1, 1, 1};
     CUresult r = g_encode(tm, HM_TMA_DTYPE, 3, const_cast<void*>(x), dims, strides,
                           box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -154,6 +154,19 @@ static bool finish_dense(Net& net, DenseLayer& L, const std::vector<act_t>& w,
     }
     return make_tm_weights(&L.tm_w, L.w, L.n_rows, L.ksize * L.ksize * L.cpad);
 }
+// 3x3, 64 < cin <= 80: the tap-packed copy for cconv3_kernel<PACKED> (layout in hm_net.h / hm_cconv.cuh)
+static bool pack_conv_tap_packed(Net& net, DenseLayer& L, const float* w) {
+    std::vector<act_t> packed(static_cast<size_t>(L.n_rows) * 768, float_to_act(0.0f));
+    for (int o = 0; o < L.cout; ++o)
+        for (int c = 0; c < L.cin; ++c)
+            for (int ky = 0; ky < 3; ++ky)
+                for (int kx = 0; kx < 3; ++kx) {
+                    const int col = kx * 256 + (c < 64 ? ky * 64 + c : 192 + ky * 16 + (c - 64));
+                    packed[static_cast<size_t>(o) * 768 + col] = float_to_act(w[(static_cast<size_t>(o) * L.cin + c) * 9 + ky * 3 + kx]);
+                }
+    L.w_tap = upload(net, packed);
+    return L.w_tap != nullptr && make_tm_weights(&L.tm_w_tap, L.w_tap, L.n_rows, 768);
+}
 // w: fp32 [cout][cin][k][k]; K per tap is padded to a multiple of 128 (cgemm stages hold two
 // 64-channel blocks).
 static bool make_dense_raw(Net& net, DenseLayer& L, const std::string& name, const float* w, int cout,
@@ -170,6 +183,7 @@ static bool make_dense_raw(Net& net, DenseLayer& L, const std::string& name, con
     std::vector<float> bias;
     if (b) bias.assign(b, b + cout);
     net.param_count += static_cast<size_t>(cout) * cin * ksize * ksize + (b ? cout : 0);
+    if (ksize == 3 && cin > 64 && cin <= 80 && !pack_conv_tap_packed(net, L, w)) return false;
     return finish_dense(net, L, packed, b ? &bias : nullptr);
 }
 static bool make_dense(Net& net, DenseLayer& L, const std::string& name, const HvmwTensor* w,
@@ -490,8 +504,10 @@ static bool kernels_prepare() {
     std::call_once(once, []() {
         ok = cuda_ok(cudaFuncSetAttribute(cgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CG_SMEM),
                      "cudaFuncSetAttribute(cgemm)") &&
-             cuda_ok(cudaFuncSetAttribute(cconv3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CC_SMEM),
+             cuda_ok(cudaFuncSetAttribute(cconv3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CC_SMEM),
                      "cudaFuncSetAttribute(cconv3)") &&
+             cuda_ok(cudaFuncSetAttribute(cconv3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CC_SMEM),
+                     "cudaFuncSetAttribute(cconv3 packed)") &&
              cuda_ok(cudaFuncSetAttribute(trunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM),
                      "cudaFuncSetAttribute(trunk)") &&
              cuda_ok(cudaFuncSetAttribute(lgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -627,7 +643,16 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
         int n_sm = 148;
         cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
         const int cgrid = std::min(grid, n_sm);
-        op.launch = [p, tm_w, tm_x, cgrid](cudaStream_t s) { cconv3_kernel<<<cgrid, CC_THREADS, CC_SMEM, s>>>(p, tm_w, tm_x); };
+        if (L.w_tap != nullptr && getenv("HM_NO_TAP_PACKED") == nullptr) {
+            CUtensorMap tm_x16;   // 16 channels of ONE position: the rows of the gathered K tile
+            if (!make_tm_act3(&tm_x16, io.in, io.in_n, io.in_C, io.in_stride_ch, 16, 1)) return false;
+            const CUtensorMap tm_wt = L.tm_w_tap;
+            op.launch = [p, tm_wt, tm_x, tm_x16, cgrid](cudaStream_t s) {
+                cconv3_kernel<true><<<cgrid, CC_THREADS, CC_SMEM, s>>>(p, tm_wt, tm_x, tm_x16);
+            };
+        } else {
+            op.launch = [p, tm_w, tm_x, cgrid](cudaStream_t s) { cconv3_kernel<false><<<cgrid, CC_THREADS, CC_SMEM, s>>>(p, tm_w, tm_x, tm_x); };
+        }
         ops.push_back(std::move(op));
         return true;
     }

@@ -46,6 +46,10 @@ struct DenseLayer {            // one tcgen05 implicit-GEMM convolution (hm_cgem
     act_t* w = nullptr;        // [n_rows][taps*cpad], K-major
     float* bias = nullptr;     // [cout] or null
     CUtensorMap tm_w;
+    // 3x3 layers with 64 < cin <= 80 (the stem): second copy packed for cconv3_kernel<PACKED> (hm_cconv.cuh),
+    // [n_rows][kx][256]: channels 0-63 of ky = 0, 1, 2, then channels 64-79 of the three ky, then 16 zero columns
+    act_t* w_tap = nullptr;
+    CUtensorMap tm_w_tap;
     double macs_per_pos() const { return 64.0 * cin * cout * ksize * ksize; }
 };
 struct Block {                 // one bottleneck block inside the trunk kernel (hm_trunk.cuh)
