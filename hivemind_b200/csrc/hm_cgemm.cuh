@@ -44,6 +44,9 @@ struct CgemmParams {
     int stages;         // ring depth (1..CG_STAGES); shallow-K 1x1 layers use 1 so that 3 CTAs share an SM
     int n_items;        // cconv3_kernel (hm_cconv.cuh): (position tile, 128-row output block) work items
     int trace;          // -DHM_BRINGUP builds only: CTA 0 of a cconv3_kernel launch logs its timeline
+    // lgemm_kernel only (hm_lgemm.cuh)
+    int kp_in2;              // K pairs kp >= kp_in2 are read from the second input tensor (channel (kp - kp_in2) * 128 ..); -1: none
+    const float* post_add;   // [out_channels][64] fp32, added AFTER the activation (token embeddings), or nullptr
 };
 
 constexpr int CG_THREADS = 192;

@@ -239,6 +239,25 @@ static bool build_crossboard(Net& net, const HvmwBlob& blob) {
         if (!net.pos_emb) return false;
     }
     if (!(net.board_emb = upload_tensor(net, T("board_emb"), 2 * D, "board_emb"))) return false;
+    {   // folded token projection: [384][384 trunk | 74 planes] + the post-activation embedding table
+        const HvmwTensor *p0 = T("tok0.wp"), *p1 = T("tok1.wp"), *b0 = T("tok0.b"), *b1 = T("tok1.b");
+        const HvmwTensor *pe = T("pos_emb"), *be = T("board_emb");
+        constexpr int KF = C + 2 * BC;
+        std::vector<float> wf(static_cast<size_t>(2) * D * KF, 0.0f), bb(2 * D), post(static_cast<size_t>(2) * D * 64);
+        for (int b = 0; b < 2; ++b)
+            for (int o = 0; o < D; ++o) {
+                float* row = wf.data() + static_cast<size_t>(b * D + o) * KF;
+                std::copy(stacked.begin() + static_cast<size_t>(b * D + o) * C, stacked.begin() + static_cast<size_t>(b * D + o + 1) * C, row);
+                const float* wp = (b ? p1 : p0)->data + static_cast<size_t>(o) * BC;
+                std::copy(wp, wp + BC, row + C + b * BC);
+                bb[b * D + o] = (b ? b1 : b0)->data[o];
+                for (int sq = 0; sq < 64; ++sq) post[static_cast<size_t>(b * D + o) * 64 + sq] = pe->data[sq * D + o] + be->data[b * D + o];
+            }
+        const size_t before = net.param_count;
+        if (!make_dense_raw(net, net.tok_fold, "tokens.fold", wf.data(), 2 * D, KF, 1, bb.data())) return false;
+        net.param_count = before;   // the same parameters were counted above
+        if (!(net.tok_post = upload(net, post))) return false;
+    }
     if (!(net.ctx_role = upload_tensor(net, T("ctx_role"), 7 * D, "ctx_role"))) return false;
     if (!(net.pocket_w = upload_tensor(net, T("pocket.w"), D * 5, "pocket.w"))) return false;
     if (!(net.pocket_b = upload_tensor(net, T("pocket.b"), D, "pocket.b"))) return false;
@@ -590,6 +609,11 @@ struct DenseIO {
     int act = 0;
     const act_t* residual = nullptr;
     const char* suffix = "";
+    // lgemm only: the channels beyond in_C come from a second tensor [in_n][in2_C][64] (its own 128-channel K pair),
+    // and post_add[out channel][64] (fp32) is added after the activation
+    const act_t* in2 = nullptr;
+    int in2_C = 0;
+    const float* post_add = nullptr;
 };
 static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseIO& io) {
     CUtensorMap tm_x;
@@ -612,6 +636,8 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
     // a 1x1 layer has only Cpad/128 <= 3 stage loads per CTA: a deep ring buys nothing, three
     // co-resident CTAs (64 KB each, 128 TMEM columns) overlap one CTA's epilogue with another's MMAs
     p.stages = L.ksize == 1 ? 1 : CG_STAGES;
+    p.kp_in2 = -1;
+    p.post_add = io.post_add;
     const int smem = p.stages == 1 ? cg_smem_bytes(1, 1) : CG_SMEM;
     const int grid = (io.in_n / 2) * p.m_blocks;
     const CUtensorMap tm_w = L.tm_w;
@@ -628,8 +654,18 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
         cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
         const dim3 lgrid(static_cast<unsigned>(std::max(1, std::min(n_tiles, n_sm / p.m_blocks))), static_cast<unsigned>(p.m_blocks));
         const int lsmem = lg_smem_bytes(kpairs);
-        op.launch = [p, tm_w, tm_x, lgrid, lsmem, n_tiles](cudaStream_t s) {
-            lgemm_kernel<<<lgrid, LG_THREADS, lsmem, s>>>(p, n_tiles, tm_w, tm_x);
+#ifdef HM_BRINGUP
+        if (const char* t = getenv("HM_CG_TRACE")) p.trace = (L.name + io.suffix) == t ? 1 : 0;
+#endif
+        CUtensorMap tm_o = tm_x, tm_x2 = tm_x;   // 16-bit outputs leave through a staging tile and TMA stores (hm_lgemm.cuh)
+        if (!io.out_f32 && !make_tm_act3(&tm_o, io.out, io.in_n, p.out_channels)) return false;
+        if (io.in2 != nullptr) {
+            if (io.in_C % 128 != 0) { set_error("lgemm: the first input of a two-input layer must fill whole K pairs"); return false; }
+            if (!make_tm_act3(&tm_x2, io.in2, io.in_n, io.in2_C)) return false;
+            p.kp_in2 = io.in_C / 128;
+        }
+        op.launch = [p, tm_w, tm_x, tm_o, tm_x2, lgrid, lsmem, n_tiles](cudaStream_t s) {
+            lgemm_kernel<<<lgrid, LG_THREADS, lsmem, s>>>(p, n_tiles, tm_w, tm_x, tm_o, tm_x2);
         };
         ops.push_back(std::move(op));
         return true;
@@ -656,6 +692,7 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
         ops.push_back(std::move(op));
         return true;
     }
+    if (io.in2 != nullptr || io.post_add != nullptr) { set_error("two-input / post-add layers need the lgemm path"); return false; }
     op.launch = [p, tm_w, tm_x, grid, smem](cudaStream_t s) {
         cgemm_kernel<<<grid, CG_THREADS, smem, s>>>(p, tm_w, tm_x);
     };
@@ -754,14 +791,23 @@ static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int 
     // X1/X2: trunk part of both token projections on the tensor cores, the 37 board planes,
     // BN bias, ReLU and the embeddings in the follow-up kernel
     {
+        const act_t* planes = w.d_planes;
+        if (getenv("HM_NO_TOKFOLD") == nullptr && getenv("HM_NO_LGEMM") == nullptr && B / 2 >= 148) {
+            // ONE GEMM: the 74 planes are the fourth K pair (second input tensor), bias + ReLU + embedding table in the
+            // epilogue; no fp32 intermediate, no token_embed_kernel
+            DenseIO io;
+            io.in = w.d_trunk; io.in_n = B; io.in_C = 384; io.out = w.d_tok[0]; io.act = 1;
+            io.in2 = planes; io.in2_C = HM_NB_INPUT_CHANNELS; io.post_add = net.tok_post;
+            if (!add_dense_io(ops, net.tok_fold, io)) return false;
+        } else {
         DenseIO io;
         io.in = w.d_trunk; io.in_n = B; io.in_C = 384; io.out = w.d_tokpre; io.out_f32 = true;
         if (!add_dense_io(ops, net.tok_proj, io)) return false;
         const float *pre = w.d_tokpre, *wp = net.tok_wp, *tb = net.tok_bias, *pe = net.pos_emb, *be = net.board_emb;
-        const act_t* planes = w.d_planes;
         act_t* tok = w.d_tok[0];
         add_simple(ops, "tokens.embed", "tokens", nb * 384 * 64 * 6.0,
                    [=](cudaStream_t s) { launch_token_embed(pre, planes, wp, tb, pe, be, tok, B, s); });
+        }
         const float *pw = net.pocket_w, *pb = net.pocket_b, *sw = net.scalar_w, *sb = net.scalar_b, *role = net.ctx_role;
         float* ctx = w.d_ctx;
         add_simple(ctx_ops, "ctx.tokens", "tokens", nb * 7 * 192 * 4.0,

@@ -94,6 +94,11 @@ struct Net {
     // crossboard-risev33 only (arch 1)
     DenseLayer tok_proj;          // 1x1 384 -> 384: trunk part of both board token projections stacked
     float *tok_wp = nullptr, *tok_bias = nullptr;      // [2][192][37], [2][192]
+    // the whole board-token projection as ONE GEMM (rise_mobile_v3.py:374-385): K = 384 trunk channels + the 74 input
+    // planes (board 0's rows see planes 0-36, board 1's rows planes 37-73, zeros elsewhere), bias = tok_bias, ReLU,
+    // then + tok_post[row][sq] = pos_emb_t[row % 192][sq] + board_emb[row]
+    DenseLayer tok_fold;
+    float* tok_post = nullptr;                         // [384][64]
     float *pos_emb = nullptr, *board_emb = nullptr, *ctx_role = nullptr;
     float *pocket_w = nullptr, *pocket_b = nullptr, *scalar_w = nullptr, *scalar_b = nullptr;
     std::vector<XLayer> xlayers;

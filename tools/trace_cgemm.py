@@ -1,5 +1,5 @@
 """Bring-up: per-item timeline of CTA 0 of one cgemm launch (build with HM_EXTRA_NVCC_FLAGS=-DHM_BRINGUP).
-usage: HM_CG_TRACE=<op name> python tools/trace_cgemm.py     (op names: stem, policy.shared, ...)"""
+usage: HM_CG_TRACE=<op name> python tools/trace_cgemm.py [arch] [batch]    (op names: stem, policy.shared, xl0.fc1 ...)"""
 import ctypes as C
 import os
 import sys
@@ -13,10 +13,11 @@ from hivemind_b200 import _lib, weights as W  # noqa: E402
 from hivemind_b200.engine import Engine  # noqa: E402
 
 CAP = 512
-B = 512
+ARCH = sys.argv[1] if len(sys.argv) > 1 else "risev33"
+B = int(sys.argv[2]) if len(sys.argv) > 2 else 512
 pk, mv, offs = bench.workload(B)
 eng = Engine(0, B, 1)
-assert eng.loadNetworkFromMemory(W.random_hvmw(seed=0))
+assert eng.loadNetworkFromMemory(W.random_hvmw(seed=0, arch=W.ARCH_CROSSBOARD_RISEV33 if ARCH == "crossboard" else W.ARCH_RISEV33))
 L = _lib.load()
 for _ in range(5):
     assert eng.evaluatePositions(pk, mv, offs, 0) is not None
@@ -44,7 +45,7 @@ ends = [t for tag, t in mma if tag == 4]
 epi_w = [t for tag, t in roles[2] if tag == 2]
 epi_d = [t for tag, t in roles[2] if tag == 3]
 epi_e = [t for tag, t in roles[2] if tag == 4]
-for i in range(len(ends)):
+for i in range(min(len(ends), len(epi_e), 12)):
     print(f"item {i}: wait drained {ready[i] - starts[i]:6d}  issue {ends[i] - ready[i]:6d}  "
           f"| accum seen +{epi_w[i] - ends[i]:5d}  drain {epi_d[i] - epi_w[i]:5d}  stores {epi_e[i] - epi_d[i]:5d}")
 if ends:
