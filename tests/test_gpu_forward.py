@@ -3,6 +3,8 @@
 Tolerances (north_star): max |dvalue| <= 1e-2, policy KL(ref || ours) <= 1e-3 over the
 legal-move distribution, against the reference PyTorch fp32 forward (golden fixture produced by
 the reference model itself, tests/golden/forward_risev33.npz) and against the fp32 oracle."""
+import os
+
 import numpy as np
 import pytest
 
@@ -420,6 +422,51 @@ def test_crossboard_full_size_batch1024_matches_reference_golden(gold_positions,
     priors, values, raw = e.evaluatePositions(pk, mv, offs)
     _assert_rows_match_golden(priors, raw, gold_cross, g, 4, VALUE_TOL, KL_TOL, 1.5e-2)
     e.close()
+
+
+@pytest.mark.parametrize("arch,batch,base,switches,vtol,ktol", [
+    # persistent 3x3 kernels vs the one-CTA-per-tile kernels, same K order: the same MMAs in the same order
+    ("risev33", 512, ("HM_NO_TAP_PACKED",), ("HM_NO_CCONV", "HM_NO_PCONV"), 0.0, 0.0),
+    # tap-packed stem vs 128 K values per tap: another fp32 summation order in the first layer, which moves a few 16-bit
+    # roundings of its outputs; the 15 blocks behind it carry that to ~1e-3 in the value (parity bar: 1e-2)
+    ("risev33", 512, (), ("HM_NO_TAP_PACKED",), 3e-3, 1e-4),
+    # one-GEMM board-token projection (16-bit plane weights, no fp32 intermediate) vs GEMM + token_embed_kernel
+    ("crossboard", 1024, ("HM_NO_TAP_PACKED",), ("HM_NO_TOKFOLD",), 3e-3, 1e-4),
+])
+def test_persistent_and_fused_kernels_match_the_kernels_they_replace(arch, batch, base, switches, vtol, ktol, gold_positions):
+    """The opt-out switches select the previous kernels when the layer program is built: same inputs, both programs.
+    (The golden-fixture tests above hold the default program to the reference; this one pins the programs to each other.)"""
+    from hivemind_b200 import weights as W
+    from hivemind_b200.engine import Engine
+
+    g = gold_positions
+    blob_ = W.random_hvmw(seed=0, arch=W.ARCH_CROSSBOARD_RISEV33 if arch == "crossboard" else W.ARCH_RISEV33)
+    pk, mv, offs = _tile(g, batch // 256)
+
+    def run():
+        e = Engine(0, batch, 1)
+        try:
+            assert e.loadNetworkFromMemory(blob_)
+            return tuple(np.array(a) for a in e.evaluatePositions(pk, mv, offs))   # copies: the results are views of
+        finally:                                                                   # engine-owned pinned memory
+            e.close()
+
+    assert not any(k in os.environ for k in base + switches)
+    try:
+        for k in base:
+            os.environ[k] = "1"
+        new = run()
+        for k in switches:
+            os.environ[k] = "1"
+        old = run()
+    finally:
+        for k in base + switches:
+            os.environ.pop(k, None)
+    assert np.abs(new[2][:, 0] - old[2][:, 0]).max() <= vtol      # raw value
+    assert np.abs(new[2][:, 4] - old[2][:, 4]).max() <= vtol      # moves left
+    assert _max_kl(new[0], old[0], offs) <= ktol
+    if vtol == 0.0:
+        assert np.array_equal(new[0], old[0])
 
 
 def test_crossboard_reference_shaped_half_path(cross_engine, oracle, gold_positions, gold_cross):
