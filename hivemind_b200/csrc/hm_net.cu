@@ -517,21 +517,32 @@ static bool host_alloc(Worker& w, T** p, size_t count) {
     return true;
 }
 
+// Opt-in to > 48 KB of dynamic shared memory is a per-DEVICE function attribute: set once per device a worker is built on
+// (a process may hold engines on several GPUs, as the reference's multi-GPU self-play does with one Engine per device).
+static int current_sm_count() {
+    int dev = 0, n_sm = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    return n_sm;
+}
 static bool kernels_prepare() {
-    static std::once_flag once;
-    static bool ok = false;
-    std::call_once(once, []() {
-        ok = cuda_ok(cudaFuncSetAttribute(cgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CG_SMEM),
-                     "cudaFuncSetAttribute(cgemm)") &&
-             cuda_ok(cudaFuncSetAttribute(cconv3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CC_SMEM),
-                     "cudaFuncSetAttribute(cconv3)") &&
-             cuda_ok(cudaFuncSetAttribute(cconv3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CC_SMEM),
-                     "cudaFuncSetAttribute(cconv3 packed)") &&
-             cuda_ok(cudaFuncSetAttribute(trunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TR_SMEM),
-                     "cudaFuncSetAttribute(trunk)") &&
-             cuda_ok(cudaFuncSetAttribute(lgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          lg_smem_bytes(LG_MAX_KPAIRS)), "cudaFuncSetAttribute(lgemm)");
-    });
+    static std::mutex mutex;
+    static bool done[64] = {};
+    int dev = 0;
+    if (!cuda_ok(cudaGetDevice(&dev), "cudaGetDevice")) return false;
+    std::lock_guard<std::mutex> lock(mutex);
+    if (dev >= 0 && dev < 64 && done[dev]) return true;
+    auto smem = [](auto* fn, int bytes, const char* what) {
+        return cuda_ok(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes), what);
+    };
+    const bool ok = smem(cgemm_kernel, CG_SMEM, "cudaFuncSetAttribute(cgemm)") &&
+                    smem(cconv3_kernel<false>, CC_SMEM, "cudaFuncSetAttribute(cconv3)") &&
+                    smem(cconv3_kernel<true>, CC_SMEM, "cudaFuncSetAttribute(cconv3 packed)") &&
+                    smem(trunk_kernel, TR_SMEM, "cudaFuncSetAttribute(trunk)") &&
+                    smem(lgemm_kernel, lg_smem_bytes(LG_MAX_KPAIRS), "cudaFuncSetAttribute(lgemm)") &&
+                    smem(pgemm_kernel, pg_smem_bytes(160), "cudaFuncSetAttribute(pgemm)") &&
+                    smem(pconv3_kernel<160>, pc_smem_bytes(160), "cudaFuncSetAttribute(pconv3<160>)") &&
+                    smem(pconv3_kernel<80>, pc_smem_bytes(80), "cudaFuncSetAttribute(pconv3<80>)") && xboard_prepare();
+    if (ok && dev >= 0 && dev < 64) done[dev] = true;
     return ok;
 }
 
@@ -650,8 +661,7 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
     // and two TMEM accumulators (hm_lgemm.cuh) instead of one latency-bound CTA per tile; HM_NO_LGEMM=1 opts out
     const int kpairs = p.kblocks / 2, n_tiles = io.in_n / 2;
     if (L.ksize == 1 && L.cout >= 128 && kpairs <= LG_MAX_KPAIRS && n_tiles >= 148 && getenv("HM_NO_LGEMM") == nullptr) {
-        int n_sm = 148;
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
+        const int n_sm = current_sm_count();
         const dim3 lgrid(static_cast<unsigned>(std::max(1, std::min(n_tiles, n_sm / p.m_blocks))), static_cast<unsigned>(p.m_blocks));
         const int lsmem = lg_smem_bytes(kpairs);
 #ifdef HM_BRINGUP
@@ -676,9 +686,7 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
 #ifdef HM_BRINGUP
         if (const char* t = getenv("HM_CG_TRACE")) p.trace = (L.name + io.suffix) == t ? 1 : 0;
 #endif
-        int n_sm = 148;
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
-        const int cgrid = std::min(grid, n_sm);
+        const int cgrid = std::min(grid, current_sm_count());
         if (L.w_tap != nullptr && getenv("HM_NO_TAP_PACKED") == nullptr) {
             CUtensorMap tm_x16;   // 16 channels of ONE position: the rows of the gathered K tile
             if (!make_tm_act3(&tm_x16, io.in, io.in_n, io.in_C, io.in_stride_ch, 16, 1)) return false;
@@ -722,11 +730,6 @@ static bool add_narrow_io(std::vector<Op>& ops, const DenseLayer& L, const Dense
     p.out_f32 = io.out_f32 ? 1 : 0;
     if (io.residual != nullptr || io.act > 1) { set_error("pgemm: residual / GELU epilogues are not supported"); return false; }
     const int smem = pg_smem_bytes(npad);
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (!cuda_ok(cudaFuncSetAttribute(pgemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pg_smem_bytes(160)), "pgemm smem attr")) return false;
-        attr_set = true;
-    }
     const int grid = io.in_n / 2;
     Op op;
     op.name = L.name + io.suffix;
@@ -735,15 +738,7 @@ static bool add_narrow_io(std::vector<Op>& ops, const DenseLayer& L, const Dense
     op.bytes = 0;
     // persistent version (one CTA per SM walks the tiles, trunk-style issue loop, 16 epilogue warps); HM_NO_PCONV=1 opts out
     if ((npad == 160 || npad == 80) && getenv("HM_NO_PCONV") == nullptr) {
-        static bool pc_attr_set = false;
-        if (!pc_attr_set) {
-            if (!cuda_ok(cudaFuncSetAttribute(pconv3_kernel<160>, cudaFuncAttributeMaxDynamicSharedMemorySize, pc_smem_bytes(160)), "pconv3<160> smem attr") ||
-                !cuda_ok(cudaFuncSetAttribute(pconv3_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, pc_smem_bytes(80)), "pconv3<80> smem attr")) return false;
-            pc_attr_set = true;
-        }
-        int n_sm = 148;
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
-        const int n_tiles = grid, cgrid = std::min(grid, n_sm);
+        const int n_tiles = grid, cgrid = std::min(grid, current_sm_count());
         if (npad == 160) op.launch = [p, tm_w, tm_x, cgrid, n_tiles](cudaStream_t s) { pconv3_kernel<160><<<cgrid, PC_THREADS, pc_smem_bytes(160), s>>>(p, n_tiles, tm_w, tm_x); };
         else op.launch = [p, tm_w, tm_x, cgrid, n_tiles](cudaStream_t s) { pconv3_kernel<80><<<cgrid, PC_THREADS, pc_smem_bytes(80), s>>>(p, n_tiles, tm_w, tm_x); };
         ops.push_back(std::move(op));
@@ -787,7 +782,7 @@ static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int 
               dev_alloc(w, &w.d_x1, nb * 384 * 64) && dev_alloc(w, &w.d_h, nb * 768 * 64) &&
               dev_alloc(w, &w.d_fuse, nb * 384 * 64) && dev_alloc(w, &w.d_ctx, nb * 7 * 192) &&
               dev_alloc(w, &w.d_ckv, 2 * nb * 7 * 384);   // one K|V block per attention layer
-    if (!ok || !xboard_prepare()) return false;
+    if (!ok) return false;
     // X1/X2: trunk part of both token projections on the tensor cores, the 37 board planes,
     // BN bias, ReLU and the embeddings in the follow-up kernel
     {

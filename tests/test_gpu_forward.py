@@ -469,6 +469,32 @@ def test_persistent_and_fused_kernels_match_the_kernels_they_replace(arch, batch
         assert np.array_equal(new[0], old[0])
 
 
+def test_engines_on_two_devices_in_one_process(blob, gold_positions, gold_forward):
+    """The reference holds one Engine per GPU inside ONE process (multi-GPU self-play): kernel attributes, tensor maps and
+    static scratch are per device here too.  Needs a box with two GPUs (skipped on the one-GPU test box)."""
+    import torch
+
+    from hivemind_b200.engine import Engine
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    g = gold_positions
+    engines = [Engine(d, 256, 1) for d in (0, 1)]
+    try:
+        outs = []
+        for e in engines:
+            assert e.loadNetworkFromMemory(blob)
+        for e in engines:
+            outs.append(tuple(np.array(a) for a in e.evaluatePositions(g["packed"], g["moves"], g["offsets"])))
+        for priors, values, raw in outs:
+            assert np.abs(raw[:, 0] - gold_forward["value"]).max() <= VALUE_TOL
+            assert _max_kl(priors, gold_forward["priors_f32"], g["offsets"]) <= KL_TOL
+        assert all(np.array_equal(a, b) for a, b in zip(outs[0], outs[1]))
+    finally:
+        for e in engines:
+            e.close()
+
+
 def test_crossboard_reference_shaped_half_path(cross_engine, oracle, gold_positions, gold_cross):
     from hivemind_b200.engine import HalfInferenceOutputs
 
