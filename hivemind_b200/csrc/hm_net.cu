@@ -12,6 +12,7 @@
 #include "hm_cgemm.cuh"
 #include "hm_cconv.cuh"
 #include "hm_lgemm.cuh"
+#include "hm_mlp.cuh"
 #include "hm_pgemm.cuh"
 #include "hm_trunk.cuh"
 #include "hm_kernels.h"
@@ -541,7 +542,8 @@ static bool kernels_prepare() {
                     smem(lgemm_kernel, lg_smem_bytes(LG_MAX_KPAIRS), "cudaFuncSetAttribute(lgemm)") &&
                     smem(pgemm_kernel, pg_smem_bytes(160), "cudaFuncSetAttribute(pgemm)") &&
                     smem(pconv3_kernel<160>, pc_smem_bytes(160), "cudaFuncSetAttribute(pconv3<160>)") &&
-                    smem(pconv3_kernel<80>, pc_smem_bytes(80), "cudaFuncSetAttribute(pconv3<80>)") && xboard_prepare();
+                    smem(pconv3_kernel<80>, pc_smem_bytes(80), "cudaFuncSetAttribute(pconv3<80>)") &&
+                    smem(mlp_kernel, ML_SMEM, "cudaFuncSetAttribute(mlp)") && xboard_prepare();
     if (ok && dev >= 0 && dev < 64) done[dev] = true;
     return ok;
 }
@@ -837,12 +839,38 @@ static bool add_crossboard(Worker& w, std::vector<Op>& ops, const Net& net, int 
         act_t* ln = w.d_nq;  // reuse
         add_simple(ops, q + "norm_mlp", "tokens", nb * 384 * 64 * 4.0,
                    [=](cudaStream_t s) { launch_token_layernorm(x1, lg, lb, ln, nullptr, nullptr, nullptr, 2 * B, s); });
+        if (getenv("HM_NO_MLPFUSE") == nullptr && B >= 148 && L.fc1.cin == ML_D && L.fc1.cout == ML_H && L.fc2.cin == ML_H &&
+            L.fc2.cout == ML_D && L.fc1.bias != nullptr && L.fc2.bias != nullptr) {
+            // fc1 -> GELU -> fc2 -> + residual as ONE kernel: the 384-wide hidden tile stays in shared memory (hm_mlp.cuh)
+            MlpParams mp{};
+            mp.n_tiles = B;   // 2B token blocks of 64, two per tile
+            mp.bias1 = L.fc1.bias;
+            mp.bias2 = L.fc2.bias;
+            mp.residual = x1;
+#ifdef HM_BRINGUP
+            if (const char* t = getenv("HM_CG_TRACE")) mp.trace = (q + "mlp") == t ? 1 : 0;
+#endif
+            CUtensorMap tm_lx, tm_lo;
+            if (!make_tm_act3(&tm_lx, ln, 2 * B, ML_D) || !make_tm_act3(&tm_lo, tout, 2 * B, ML_D)) return false;
+            const CUtensorMap tm_w1 = L.fc1.tm_w, tm_w2 = L.fc2.tm_w;
+            const int mgrid = std::min(B, current_sm_count());
+            Op op;
+            op.name = q + "mlp";
+            op.klass = "dense";
+            op.flops = 2.0 * (L.fc1.macs_per_pos() + L.fc2.macs_per_pos()) * 2 * B;
+            op.bytes = 0;
+            op.launch = [mp, tm_w1, tm_w2, tm_lx, tm_lo, mgrid](cudaStream_t s) {
+                mlp_kernel<<<mgrid, ML_THREADS, ML_SMEM, s>>>(mp, tm_w1, tm_w2, tm_lx, tm_lo);
+            };
+            ops.push_back(std::move(op));
+        } else {
         io = DenseIO();
         io.in = ln; io.in_n = 2 * B; io.in_C = 192; io.out = w.d_h; io.act = 2;
         if (!add_dense_io(ops, L.fc1, io)) return false;
         io = DenseIO();
         io.in = w.d_h; io.in_n = 2 * B; io.in_C = 384; io.out = tout; io.residual = x1;
         if (!add_dense_io(ops, L.fc2, io)) return false;
+        }
         cur ^= 1;
         w.debug_views["tokens" + std::to_string(l + 1)] = {tout, {B, 384 * 64, 0}};
     }

@@ -432,6 +432,9 @@ def test_crossboard_full_size_batch1024_matches_reference_golden(gold_positions,
     ("risev33", 512, (), ("HM_NO_TAP_PACKED",), 3e-3, 1e-4),
     # one-GEMM board-token projection (16-bit plane weights, no fp32 intermediate) vs GEMM + token_embed_kernel
     ("crossboard", 1024, ("HM_NO_TAP_PACKED",), ("HM_NO_TOKFOLD",), 3e-3, 1e-4),
+    # fc1 -> GELU -> fc2 -> + residual as one kernel (hidden tile in shared memory) vs two Linear launches: the same
+    # 16-bit hidden values, the same K order
+    ("crossboard", 1024, (), ("HM_NO_MLPFUSE",), 0.0, 0.0),
 ])
 def test_persistent_and_fused_kernels_match_the_kernels_they_replace(arch, batch, base, switches, vtol, ktol, gold_positions):
     """The opt-out switches select the previous kernels when the layer program is built: same inputs, both programs.
