@@ -183,7 +183,7 @@ __device__ __forceinline__ void trunk_chunk(const float* __restrict__ par, int r
     }
     const float b1 = __ldg(par + r), bd = __ldg(par + 128 + r);
     TR_MARK(2, 1);
-    tr_wait_full(&bars[TB_D1_FULL], d1_n);
+    mbar_wait_backoff(&bars[TB_D1_FULL], d1_n & 1, 20);   // sixteen warps wait here ~1 k cycles per 3x3 chunk: off the issue slots
     tc_fence_after();
     TR_MARK(2, 2);
     float y[NR * 8];
