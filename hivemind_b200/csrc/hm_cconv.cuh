@@ -42,7 +42,8 @@ constexpr int CC_THREADS = 64 + CC_EPI_WARPS * 32;
 constexpr int CC_WTILES = 6;                 // 16 KB weight tiles [128 rows x 64 K]; pair kx = tiles 2kx, 2kx+1
 constexpr int CC_XSTAGES = 3;                // 32 KB activation stages [2 x 64 channels][2 positions][64 squares]
 constexpr int CC_X_OFF = CC_WTILES * 16384;
-constexpr int CC_BAR_OFF = CC_X_OFF + CC_XSTAGES * CG_STAGE_BYTES;
+constexpr int CC_OUT_OFF = CC_X_OFF + CC_XSTAGES * CG_STAGE_BYTES;   // 32 KB output staging tile (16-bit outputs)
+constexpr int CC_BAR_OFF = CC_OUT_OFF + CG_STAGE_BYTES;
 constexpr int CC_SMEM = CC_BAR_OFF + 256 + 1024;
 enum {
     CB_X_FULL = 0,                           // 3
@@ -63,7 +64,7 @@ enum {
 template <bool PACKED>
 __global__ void __launch_bounds__(CC_THREADS, 1)
 cconv3_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
-              const __grid_constant__ CUtensorMap tmX16) {
+              const __grid_constant__ CUtensorMap tmX16, const __grid_constant__ CUtensorMap tmO) {
     extern __shared__ uint8_t cc_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cc_smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + CC_BAR_OFF);
@@ -227,6 +228,13 @@ cconv3_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW, cons
         const int q = warp & 3;                  // a warp may only touch TMEM lanes 32 * (warp % 4) ..
         const int c = (warp - 2) >> 2;           // chunk: position c >> 1, squares 32 * (c & 1) ..
         const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32;
+        // 16-bit outputs whose valid channels end on a 64-channel box boundary leave through a staging tile in the input
+        // boxes' swizzled layout and two TMA stores (direct 16-byte stores put the 32 lanes of an instruction in 32
+        // different 128-byte lines, ~8 B/clk per SM: the stem's items were bound by them)
+        const bool staged = !p.out_f32 && (p.n_valid & 63) == 0;
+        const bool storer = warp == 2 && lane == 0;
+        const int rl = q * 32 + lane;
+        uint8_t* my_row = smem + CC_OUT_OFF + (rl >> 6) * 16384 + (c >> 1) * 8192 + (rl & 63) * 128;
         uint32_t it = 0;
         for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
             const int tile = item / p.m_blocks;
@@ -234,12 +242,6 @@ cconv3_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW, cons
             const bool valid = ch < p.n_valid;
             const float bias = (valid && p.bias != nullptr) ? __ldg(p.bias + ch) : 0.0f;
             const size_t row = (static_cast<size_t>(tile * 2 + (c >> 1)) * p.out_channels + ch) * 64 + (c & 1) * 32;
-            uint4 res[4];   // the residual row is requested BEFORE the wait for the accumulators
-            if (valid && p.residual != nullptr) {
-                const uint4* rr = reinterpret_cast<const uint4*>(p.residual + row);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) res[j] = __ldg(rr + j);
-            }
             if (warp == 2) CC_MARK(2, 1);
             mbar_wait_backoff(&bars[CB_ACCUM], it & 1, 64);
             tc_fence_after();
@@ -266,46 +268,53 @@ cconv3_kernel(const CgemmParams p, const __grid_constant__ CUtensorMap tmW, cons
             __syncwarp();
             if (lane == 0) mbar_arrive(&bars[CB_DRAINED]);   // this warp's part is in registers
             if (warp == 2) CC_MARK(2, 3);
-            if (valid) {
-                if (p.residual != nullptr) {
+            // (residual adds and GELU are cgemm_kernel's: the host routes no such layer here)
+            if (p.relu == 1) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const uint4 u4 = res[j];
-                        const uint32_t w4[4] = {u4.x, u4.y, u4.z, u4.w};
-#pragma unroll
-                        for (int t = 0; t < 4; ++t) {
-                            const float2 f = unpack_act2(w4[t]);
-                            v[8 * j + 2 * t] += f.x;
-                            v[8 * j + 2 * t + 1] += f.y;
-                        }
-                    }
-                }
-                if (p.relu == 1) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
-                } else if (p.relu == 2) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = 0.5f * v[j] * (1.0f + erff(v[j] * 0.70710678118654752f));
-                }
-                if (p.out_f32) {
+                for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+            }
+            if (p.out_f32) {
+                if (valid) {
                     float4* o = reinterpret_cast<float4*>(static_cast<float*>(p.out) + row);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                } else {
-                    uint4* o = reinterpret_cast<uint4*>(static_cast<act_t*>(p.out) + row);
+                }
+            } else {
+                uint4 w[4];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        uint4 w;
-                        w.x = pack_act2(v[8 * j + 0], v[8 * j + 1]);
-                        w.y = pack_act2(v[8 * j + 2], v[8 * j + 3]);
-                        w.z = pack_act2(v[8 * j + 4], v[8 * j + 5]);
-                        w.w = pack_act2(v[8 * j + 6], v[8 * j + 7]);
-                        o[j] = w;
+                for (int j = 0; j < 4; ++j) {
+                    w[j].x = pack_act2(v[8 * j + 0], v[8 * j + 1]);
+                    w[j].y = pack_act2(v[8 * j + 2], v[8 * j + 3]);
+                    w[j].z = pack_act2(v[8 * j + 4], v[8 * j + 5]);
+                    w[j].w = pack_act2(v[8 * j + 6], v[8 * j + 7]);
+                }
+                if (!staged) {
+                    if (valid) {
+                        uint4* o = reinterpret_cast<uint4*>(static_cast<act_t*>(p.out) + row);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) o[j] = w[j];
+                    }
+                } else {   // kernel-uniform: all sixteen warps take the two barriers
+                    if (storer) bulk_wait_group_read0();   // the previous item's stores have read the staging tile
+                    named_bar_sync(1, CC_EPI_WARPS * 32);
+                    if (valid) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            *reinterpret_cast<uint4*>(my_row + ((((c & 1) * 4 + j) ^ (rl & 7)) << 4)) = w[j];
+                    }
+                    fence_proxy_async_smem();
+                    named_bar_sync(2, CC_EPI_WARPS * 32);
+                    if (storer) {
+                        const int r0 = (item - tile * p.m_blocks) * 128;
+                        if (r0 < p.n_valid) tma_store_3d(&tmO, smem + CC_OUT_OFF, 0, r0, tile * 2);
+                        if (r0 + 64 < p.n_valid) tma_store_3d(&tmO, smem + CC_OUT_OFF + 16384, 0, r0 + 64, tile * 2);
+                        bulk_commit_group();
                     }
                 }
             }
             if (warp == 2) CC_MARK(2, 4);
         }
+        if (storer) bulk_wait_group0();
     }
     tc_fence_before();
     __syncthreads();

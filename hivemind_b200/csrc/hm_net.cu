@@ -683,21 +683,23 @@ static bool add_dense_io(std::vector<Op>& ops, const DenseLayer& L, const DenseI
         return true;
     }
     // 3x3 layers: one persistent CTA per SM walks the (tile, output block) work items (hm_cconv.cuh); HM_NO_CCONV=1 opts out
-    if (L.ksize == 3 && p.residual == nullptr && getenv("HM_NO_CCONV") == nullptr) {
+    if (L.ksize == 3 && p.residual == nullptr && io.act <= 1 && getenv("HM_NO_CCONV") == nullptr) {
         p.n_items = grid;
 #ifdef HM_BRINGUP
         if (const char* t = getenv("HM_CG_TRACE")) p.trace = (L.name + io.suffix) == t ? 1 : 0;
 #endif
         const int cgrid = std::min(grid, current_sm_count());
+        CUtensorMap tm_o = tm_x;   // 16-bit outputs leave through a staging tile and TMA stores
+        if (!io.out_f32 && !make_tm_act3(&tm_o, io.out, io.in_n, p.out_channels)) return false;
         if (L.w_tap != nullptr && getenv("HM_NO_TAP_PACKED") == nullptr) {
             CUtensorMap tm_x16;   // 16 channels of ONE position: the rows of the gathered K tile
             if (!make_tm_act3(&tm_x16, io.in, io.in_n, io.in_C, io.in_stride_ch, 16, 1)) return false;
             const CUtensorMap tm_wt = L.tm_w_tap;
-            op.launch = [p, tm_wt, tm_x, tm_x16, cgrid](cudaStream_t s) {
-                cconv3_kernel<true><<<cgrid, CC_THREADS, CC_SMEM, s>>>(p, tm_wt, tm_x, tm_x16);
+            op.launch = [p, tm_wt, tm_x, tm_x16, tm_o, cgrid](cudaStream_t s) {
+                cconv3_kernel<true><<<cgrid, CC_THREADS, CC_SMEM, s>>>(p, tm_wt, tm_x, tm_x16, tm_o);
             };
         } else {
-            op.launch = [p, tm_w, tm_x, cgrid](cudaStream_t s) { cconv3_kernel<false><<<cgrid, CC_THREADS, CC_SMEM, s>>>(p, tm_w, tm_x, tm_x); };
+            op.launch = [p, tm_w, tm_x, tm_o, cgrid](cudaStream_t s) { cconv3_kernel<false><<<cgrid, CC_THREADS, CC_SMEM, s>>>(p, tm_w, tm_x, tm_x, tm_o); };
         }
         ops.push_back(std::move(op));
         return true;
