@@ -9,7 +9,7 @@
 // As two lgemm launches the hidden tensor (n2 x 384 x 64 x 2 B = 100 MB at B = 1024) was written to HBM and read back:
 // fc1 0.064 ms + fc2 0.062 ms per layer, both bound by the bytes they can keep in flight per SM.  Here it never leaves
 // the SM.  One persistent CTA per SM walks the 128-token tiles; both weight matrices (336 KB) stream through a
-// 4-tile ring per tile, from L2.
+// 5-tile ring per tile, from L2.
 //
 // Shared memory: Hs 6 boxes x 16 KB ([2 positions][64 channels][64 squares], 128-byte swizzled, = the layout of an
 // input box; boxes 0-2 double as the output staging tile), X 3 boxes (the LayerNorm-ed tokens of the tile), weight
